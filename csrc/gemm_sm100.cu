@@ -1,0 +1,532 @@
+// tcgen05 / TMEM GEMM for sm_100a, fed by TMA, persistent and warp-specialised.
+//
+//   warp 0      : TMA producer (one elected lane) — fills a ring of NUM_STAGES smem stages
+//   warp 1      : TMEM allocator + MMA issuer (one elected lane issues tcgen05.mma)
+//   warps 2..9  : epilogue — tcgen05.ld the fp32 accumulator out of TMEM, apply
+//                 alpha / bias / GELU / residual-add / GELU', convert to bf16, store
+//
+// The accumulator is double-buffered in TMEM (2 x BLOCK_N columns) so the epilogue of tile
+// i overlaps the MMAs of tile i+1.  Operands may be K-major or MN-major ("transposed");
+// both use 128-byte-swizzled smem tiles written by TMA and described to the tensor core by
+// UMMA shared-memory descriptors, so forward (X·Wᵀ), dgrad (dY·W), wgrad (dYᵀ·X) and the
+// batched attention products all run through this one kernel with no explicit transposes.
+//
+// Replaces the cuBLAS GEMMs implied by model.fit() in the reference
+// (scripts/train.py:145; SURVEY.md §2.4 K2/K4/K5/K6 and the K3 matmuls).
+#include <mutex>
+#include <string>
+#include <unordered_map>
+
+#include "../include/hstd_b200.h"
+#include "common.cuh"
+#include "sm100_ptx.cuh"
+
+namespace hstd {
+
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_K = 64;  // 64 bf16 = one 128-byte swizzle row
+constexpr int UMMA_K = 16;
+constexpr int NUM_EPI_WARPS = 8;
+constexpr int GEMM_THREADS = (2 + NUM_EPI_WARPS) * 32;
+
+struct GemmKernelParams {
+  __nv_bfloat16* C;
+  float* Cf32;  // split-K partial output (fp32) when num_splits > 1
+  const __nv_bfloat16* bias;
+  __nv_bfloat16* aux;
+  int64_t ldc, c_bs0, c_bs1, ldaux;
+  int M, N, K;
+  int nb0, nb1;
+  int tiles_m, tiles_n;
+  int num_splits, kb_per_split;
+  int epilogue;
+  float alpha;
+};
+
+template <int BN>
+struct GemmCfg {
+  static constexpr int STAGES = BN == 256 ? 4 : (BN == 128 ? 6 : 8);
+  static constexpr size_t SMEM = 1024 /*align slack*/ + size_t(STAGES) * (BLOCK_M * BLOCK_K * 2 + BN * BLOCK_K * 2) + 256;
+};
+
+template <int BN, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                 const GemmKernelParams p) {
+  constexpr int STAGES = GemmCfg<BN>::STAGES;
+  constexpr uint32_t A_BYTES = BLOCK_M * BLOCK_K * 2;
+  constexpr uint32_t B_BYTES = BN * BLOCK_K * 2;
+  constexpr uint32_t TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;
+  constexpr uint32_t IDESC = make_idesc_bf16(BLOCK_M, BN, A_MN, B_MN);
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + STAGES * A_BYTES;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_b + STAGES * B_BYTES);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full = empty_bar + STAGES;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_b);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tmem_full[i], 1);
+      mbar_init(&tmem_empty[i], NUM_EPI_WARPS);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int tiles_per_batch = p.tiles_m * p.tiles_n * p.num_splits;
+  const int total_tiles = tiles_per_batch * p.nb0 * p.nb1;
+  const int num_kb_total = (p.K + BLOCK_K - 1) / BLOCK_K;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int z = tile / tiles_per_batch;
+        int r = tile - z * tiles_per_batch;
+        const int split = r / (p.tiles_m * p.tiles_n);
+        r -= split * (p.tiles_m * p.tiles_n);
+        const int tm = r / p.tiles_n, tn = r - tm * p.tiles_n;
+        const int z0 = z % p.nb0, z1 = z / p.nb0;
+        const int m0 = tm * BLOCK_M, n0 = tn * BN;
+        const int kb_begin = split * p.kb_per_split;
+        const int kb_end = min(num_kb_total, kb_begin + p.kb_per_split);
+        for (int kb = kb_begin; kb < kb_end; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_expect_tx(&full_bar[stage], A_BYTES + B_BYTES);
+          uint8_t* sa = smem_a + stage * A_BYTES;
+          uint8_t* sb = smem_b + stage * B_BYTES;
+          const int k0 = kb * BLOCK_K;
+          if constexpr (!A_MN) {
+            tma_load_4d(sa, &tmap_a, &full_bar[stage], k0, m0, z0, z1);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BLOCK_M / 64; ++j)
+              tma_load_4d(sa + j * (64 * BLOCK_K * 2), &tmap_a, &full_bar[stage], m0 + 64 * j, k0, z0, z1);
+          }
+          if constexpr (!B_MN) {
+            tma_load_4d(sb, &tmap_b, &full_bar[stage], k0, n0, z0, z1);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j)
+              tma_load_4d(sb + j * (64 * BLOCK_K * 2), &tmap_b, &full_bar[stage], n0 + 64 * j, k0, z0, z1);
+          }
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        int r = tile % tiles_per_batch;
+        const int split = r / (p.tiles_m * p.tiles_n);
+        const int kb_begin = split * p.kb_per_split;
+        const int kb_end = min(num_kb_total, kb_begin + p.kb_per_split);
+        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kb = kb_begin; kb < kb_end; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(smem_a + stage * A_BYTES);
+          const uint32_t b_addr = smem_u32(smem_b + stage * B_BYTES);
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+            // K-major: advance 16 elements (32 B) inside the swizzled row.
+            // MN-major: advance 16 K-rows = two 8-row groups of 1024 B.
+            const uint64_t da = A_MN ? make_smem_desc_sw128(a_addr + k * 2048, 64 * BLOCK_K * 2, 1024)
+                                     : make_smem_desc_sw128(a_addr + k * 32, 16, 1024);
+            const uint64_t db = B_MN ? make_smem_desc_sw128(b_addr + k * 2048, 64 * BLOCK_K * 2, 1024)
+                                     : make_smem_desc_sw128(b_addr + k * 32, 16, 1024);
+            umma_bf16(d_tmem, da, db, IDESC, (kb > kb_begin || k > 0) ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);  // smem stage free once these MMAs retire
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit(&tmem_full[acc]);  // accumulator complete
+        if (++acc == 2) {
+          acc = 0;
+          acc_phase ^= 1;
+        }
+      }
+    }
+  } else {
+    // ------------------------------------------------------------ epilogue warps
+    const int ew = warp - 2;             // 0..7
+    const int quarter = warp & 3;        // TMEM lane quarter this warp may read
+    const int col_half = ew >> 2;        // which half of the BN columns
+    constexpr int COLS_PER_WARP = BN / 2;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const int z = tile / tiles_per_batch;
+      int r = tile - z * tiles_per_batch;
+      const int split = r / (p.tiles_m * p.tiles_n);
+      r -= split * (p.tiles_m * p.tiles_n);
+      const int tm = r / p.tiles_n, tn = r - tm * p.tiles_n;
+      const int z0 = z % p.nb0, z1 = z / p.nb0;
+      const int row = tm * BLOCK_M + quarter * 32 + lane;
+      const int col_base = tn * BN + col_half * COLS_PER_WARP;
+
+      mbar_wait(&tmem_full[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + acc * BN + col_half * COLS_PER_WARP + (uint32_t(quarter * 32) << 16);
+      const int64_t zoff = int64_t(z0) * p.c_bs0 + int64_t(z1) * p.c_bs1;
+#pragma unroll 1
+      for (int c = 0; c < COLS_PER_WARP; c += 32) {
+        uint32_t v[32];
+        tmem_ld_32x32(t_row + c, v);
+        tmem_ld_wait();
+        const int col0 = col_base + c;
+        if (row < p.M && col0 < p.N) {
+          if (p.num_splits > 1) {
+            float* dst = p.Cf32 + (int64_t(split) * p.M + row) * p.N + col0;
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              if (col0 + j < p.N) {
+                float4 o = make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]),
+                                       __uint_as_float(v[j + 3]));
+                *reinterpret_cast<float4*>(dst + j) = o;
+              }
+            }
+          } else {
+            float f[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * p.alpha;
+            if (p.bias != nullptr) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 8) {
+                if (col0 + j < p.N) {
+                  const uint4 b = __ldg(reinterpret_cast<const uint4*>(p.bias + col0 + j));
+                  const float2 b0 = unpack_bf16x2(b.x), b1 = unpack_bf16x2(b.y), b2 = unpack_bf16x2(b.z),
+                               b3 = unpack_bf16x2(b.w);
+                  f[j] += b0.x; f[j + 1] += b0.y; f[j + 2] += b1.x; f[j + 3] += b1.y;
+                  f[j + 4] += b2.x; f[j + 5] += b2.y; f[j + 6] += b3.x; f[j + 7] += b3.y;
+                }
+              }
+            }
+            __nv_bfloat16* crow = p.C + zoff + int64_t(row) * p.ldc + col0;
+            __nv_bfloat16* auxrow = p.aux ? p.aux + zoff + int64_t(row) * p.ldaux + col0 : nullptr;
+            if (p.epilogue == HSTD_EPI_GELU) {
+              if (auxrow) {
+#pragma unroll
+                for (int j = 0; j < 32; j += 8) {
+                  if (col0 + j < p.N) {
+                    uint4 o = make_uint4(pack_bf16x2(f[j], f[j + 1]), pack_bf16x2(f[j + 2], f[j + 3]),
+                                         pack_bf16x2(f[j + 4], f[j + 5]), pack_bf16x2(f[j + 6], f[j + 7]));
+                    *reinterpret_cast<uint4*>(auxrow + j) = o;
+                  }
+                }
+              }
+#pragma unroll
+              for (int j = 0; j < 32; ++j) f[j] = gelu_erf(f[j]);
+            } else if (p.epilogue == HSTD_EPI_ADD) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 8) {
+                if (col0 + j < p.N) {
+                  const uint4 a = *reinterpret_cast<const uint4*>(auxrow + j);
+                  const float2 a0 = unpack_bf16x2(a.x), a1 = unpack_bf16x2(a.y), a2 = unpack_bf16x2(a.z),
+                               a3 = unpack_bf16x2(a.w);
+                  f[j] += a0.x; f[j + 1] += a0.y; f[j + 2] += a1.x; f[j + 3] += a1.y;
+                  f[j + 4] += a2.x; f[j + 5] += a2.y; f[j + 6] += a3.x; f[j + 7] += a3.y;
+                }
+              }
+            } else if (p.epilogue == HSTD_EPI_GELU_BWD) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 8) {
+                if (col0 + j < p.N) {
+                  const uint4 a = *reinterpret_cast<const uint4*>(auxrow + j);
+                  const float2 a0 = unpack_bf16x2(a.x), a1 = unpack_bf16x2(a.y), a2 = unpack_bf16x2(a.z),
+                               a3 = unpack_bf16x2(a.w);
+                  f[j] *= gelu_erf_grad(a0.x); f[j + 1] *= gelu_erf_grad(a0.y);
+                  f[j + 2] *= gelu_erf_grad(a1.x); f[j + 3] *= gelu_erf_grad(a1.y);
+                  f[j + 4] *= gelu_erf_grad(a2.x); f[j + 5] *= gelu_erf_grad(a2.y);
+                  f[j + 6] *= gelu_erf_grad(a3.x); f[j + 7] *= gelu_erf_grad(a3.y);
+                }
+              }
+            }
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              if (col0 + j < p.N) {
+                uint4 o = make_uint4(pack_bf16x2(f[j], f[j + 1]), pack_bf16x2(f[j + 2], f[j + 3]),
+                                     pack_bf16x2(f[j + 4], f[j + 5]), pack_bf16x2(f[j + 6], f[j + 7]));
+                *reinterpret_cast<uint4*>(crow + j) = o;
+              }
+            }
+          }
+        }
+      }
+      // All TMEM reads of this accumulator buffer are done (wait::ld above): hand it back.
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+      if (++acc == 2) {
+        acc = 0;
+        acc_phase ^= 1;
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+// fp32 split-K partials -> bf16
+__global__ void splitk_reduce_kernel(const float* __restrict__ ws, __nv_bfloat16* __restrict__ C, int64_t ldc, int M,
+                                     int N, int splits, float alpha) {
+  const int64_t n4 = int64_t(M) * N / 4;
+  for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n4; i += int64_t(gridDim.x) * blockDim.x) {
+    float4 s = reinterpret_cast<const float4*>(ws)[i];
+    for (int k = 1; k < splits; ++k) {
+      const float4 t = reinterpret_cast<const float4*>(ws)[i + k * n4];
+      s.x += t.x; s.y += t.y; s.z += t.z; s.w += t.w;
+    }
+    const int64_t e = i * 4;
+    const int row = int(e / N), col = int(e - int64_t(row) * N);
+    uint2 o = make_uint2(pack_bf16x2(s.x * alpha, s.y * alpha), pack_bf16x2(s.z * alpha, s.w * alpha));
+    *reinterpret_cast<uint2*>(C + int64_t(row) * ldc + col) = o;
+  }
+}
+
+// ------------------------------------------------------------------ host side
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode_fn() {
+  static PFN_encodeTiled fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_encodeTiled>(ptr);
+  });
+  return fn;
+}
+
+struct TmapKey {
+  const void* ptr;
+  uint64_t d0, d1, d2, d3, s1, s2, s3;
+  uint32_t b0, b1;
+  bool operator==(const TmapKey& o) const {
+    return ptr == o.ptr && d0 == o.d0 && d1 == o.d1 && d2 == o.d2 && d3 == o.d3 && s1 == o.s1 && s2 == o.s2 &&
+           s3 == o.s3 && b0 == o.b0 && b1 == o.b1;
+  }
+};
+struct TmapKeyHash {
+  size_t operator()(const TmapKey& k) const {
+    uint64_t h = reinterpret_cast<uint64_t>(k.ptr);
+    auto mix = [&h](uint64_t v) { h ^= v + 0x9e3779b97f4a7c15ull + (h << 6) + (h >> 2); };
+    mix(k.d0); mix(k.d1); mix(k.d2); mix(k.d3); mix(k.s1); mix(k.s2); mix(k.s3); mix(k.b0); mix(k.b1);
+    return size_t(h);
+  }
+};
+
+// bf16 4-D tensor map {d0 (contiguous), d1, d2, d3} with element strides s1..s3 and a
+// 128B-swizzled box of {64, box_rows, 1, 1}.
+static int get_tmap(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t d3,
+                    uint64_t s1, uint64_t s2, uint64_t s3, uint32_t box_rows) {
+  static std::mutex mu;
+  static std::unordered_map<TmapKey, CUtensorMap, TmapKeyHash> cache;
+  TmapKey key{ptr, d0, d1, d2, d3, s1, s2, s3, 64u, box_rows};
+  {
+    std::lock_guard<std::mutex> g(mu);
+    auto it = cache.find(key);
+    if (it != cache.end()) {
+      *out = it->second;
+      return 0;
+    }
+  }
+  PFN_encodeTiled enc = get_encode_fn();
+  if (!enc) return set_error(-2, "cuTensorMapEncodeTiled not available from the driver");
+  // A batch dimension of extent 1 never advances, but its stride must still be legal.
+  if (d2 <= 1) s2 = s1 * d1;
+  if (d3 <= 1) s3 = s2 * (d2 ? d2 : 1);
+  cuuint64_t dims[4] = {d0, d1, d2 ? d2 : 1, d3 ? d3 : 1};
+  cuuint64_t strides[3] = {s1 * 2, s2 * 2, s3 * 2};
+  cuuint32_t box[4] = {64, box_rows, 1, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) || (strides[0] & 15) || (strides[1] & 15) || (strides[2] & 15))
+    return set_error(-3, "gemm operand pointer/strides must be 16-byte aligned");
+  CUtensorMap m;
+  CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return set_error(-4, "cuTensorMapEncodeTiled failed (code " + std::to_string(int(r)) + ")");
+  {
+    std::lock_guard<std::mutex> g(mu);
+    cache.emplace(key, m);
+  }
+  *out = m;
+  return 0;
+}
+
+static int num_sms() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}
+
+template <int BN, bool A_MN, bool B_MN>
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmKernelParams& p, int max_ctas,
+                       cudaStream_t stream) {
+  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN>;
+  constexpr size_t smem = GemmCfg<BN>::SMEM;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+    if (e != cudaSuccess) return set_error(-5, std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e));
+    configured = true;
+  }
+  const int total = p.tiles_m * p.tiles_n * p.num_splits * p.nb0 * p.nb1;
+  int grid = num_sms();
+  if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
+  if (total < grid) grid = total;
+  kern<<<grid, GEMM_THREADS, smem, stream>>>(ta, tb, p);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return set_error(-6, std::string("gemm launch: ") + cudaGetErrorString(e));
+  return 0;
+}
+
+static int pick_block_n(int M, int N, int batches, int splits) {
+  // 256-wide tiles halve the B-operand smem traffic per FLOP; use them when they still
+  // give every SM a tile, otherwise fall back to 128 (64 for the narrow attention outputs).
+  if (N <= 64) return 64;
+  const int tm = (M + BLOCK_M - 1) / BLOCK_M;
+  if (N >= 256 && tm * ((N + 255) / 256) * batches * splits >= num_sms()) return 256;
+  return 128;
+}
+
+static int gemm_impl(const hstd_gemm_args* a, int splits, float* workspace, cudaStream_t stream) {
+  if (a->M <= 0 || a->N <= 0 || a->K <= 0) return set_error(-1, "gemm: empty problem");
+  if (a->N % 8 != 0) return set_error(-1, "gemm: N must be a multiple of 8");
+  const int nb0 = a->nb0 > 0 ? a->nb0 : 1, nb1 = a->nb1 > 0 ? a->nb1 : 1;
+  int bn = a->block_n ? a->block_n : pick_block_n(a->M, a->N, nb0 * nb1, splits);
+  if (bn != 64 && bn != 128 && bn != 256) return set_error(-1, "gemm: block_n must be 64, 128 or 256");
+
+  CUtensorMap ta, tb;
+  int rc;
+  if (!a->a_mn_major)
+    rc = get_tmap(&ta, a->A, a->K, a->M, nb0, nb1, a->lda, a->a_bs0, a->a_bs1, BLOCK_M);
+  else
+    rc = get_tmap(&ta, a->A, a->M, a->K, nb0, nb1, a->lda, a->a_bs0, a->a_bs1, 64);
+  if (rc) return rc;
+  if (!a->b_mn_major)
+    rc = get_tmap(&tb, a->B, a->K, a->N, nb0, nb1, a->ldb, a->b_bs0, a->b_bs1, bn);
+  else
+    rc = get_tmap(&tb, a->B, a->N, a->K, nb0, nb1, a->ldb, a->b_bs0, a->b_bs1, 64);
+  if (rc) return rc;
+
+  GemmKernelParams p;
+  p.C = static_cast<__nv_bfloat16*>(a->C);
+  p.Cf32 = workspace;
+  p.bias = static_cast<const __nv_bfloat16*>(a->bias);
+  p.aux = static_cast<__nv_bfloat16*>(a->aux);
+  p.ldc = a->ldc; p.c_bs0 = a->c_bs0; p.c_bs1 = a->c_bs1; p.ldaux = a->ldaux;
+  p.M = a->M; p.N = a->N; p.K = a->K; p.nb0 = nb0; p.nb1 = nb1;
+  p.tiles_m = (a->M + BLOCK_M - 1) / BLOCK_M;
+  p.tiles_n = (a->N + bn - 1) / bn;
+  const int num_kb = (a->K + BLOCK_K - 1) / BLOCK_K;
+  if (splits > num_kb) splits = num_kb;
+  p.num_splits = splits;
+  p.kb_per_split = (num_kb + splits - 1) / splits;
+  p.epilogue = a->epilogue;
+  p.alpha = a->alpha;
+  if ((a->epilogue == HSTD_EPI_ADD || a->epilogue == HSTD_EPI_GELU_BWD) && a->aux == nullptr)
+    return set_error(-1, "gemm: this epilogue needs aux");
+
+#define HSTD_GEMM_CASE(BN_)                                                                         \
+  if (bn == BN_) {                                                                                  \
+    if (!a->a_mn_major && !a->b_mn_major) return launch_gemm<BN_, false, false>(ta, tb, p, a->max_ctas, stream); \
+    if (!a->a_mn_major && a->b_mn_major) return launch_gemm<BN_, false, true>(ta, tb, p, a->max_ctas, stream);   \
+    if (a->a_mn_major && !a->b_mn_major) return launch_gemm<BN_, true, false>(ta, tb, p, a->max_ctas, stream);   \
+    return launch_gemm<BN_, true, true>(ta, tb, p, a->max_ctas, stream);                            \
+  }
+  HSTD_GEMM_CASE(64)
+  HSTD_GEMM_CASE(128)
+  HSTD_GEMM_CASE(256)
+#undef HSTD_GEMM_CASE
+  return set_error(-1, "gemm: unreachable");
+}
+
+}  // namespace hstd
+
+extern "C" HSTD_API int hstd_gemm_bf16(const hstd_gemm_args* args, void* stream) {
+  return hstd::gemm_impl(args, 1, nullptr, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" HSTD_API int64_t hstd_gemm_splitk_workspace_bytes(int M, int N, int splits) {
+  return int64_t(M) * N * splits * 4;
+}
+
+extern "C" HSTD_API int hstd_gemm_bf16_splitk(const hstd_gemm_args* args, int splits, void* workspace,
+                                     int64_t workspace_bytes, void* stream) {
+  using namespace hstd;
+  if (splits <= 1) return gemm_impl(args, 1, nullptr, static_cast<cudaStream_t>(stream));
+  if (args->nb0 > 1 || args->nb1 > 1) return set_error(-1, "splitk: batched problems are not supported");
+  if (args->epilogue != HSTD_EPI_NONE || args->bias) return set_error(-1, "splitk: only EPI_NONE without bias");
+  if (args->N % 4 != 0) return set_error(-1, "splitk: N must be a multiple of 4");
+  const int num_kb = (args->K + BLOCK_K - 1) / BLOCK_K;
+  if (splits > num_kb) splits = num_kb;
+  // kb_per_split rounding may leave trailing splits empty; shrink so every split has work.
+  const int per = (num_kb + splits - 1) / splits;
+  splits = (num_kb + per - 1) / per;
+  if (splits <= 1) return gemm_impl(args, 1, nullptr, static_cast<cudaStream_t>(stream));
+  if (workspace == nullptr || workspace_bytes < hstd_gemm_splitk_workspace_bytes(args->M, args->N, splits))
+    return set_error(-1, "splitk: workspace too small");
+  int rc = gemm_impl(args, splits, static_cast<float*>(workspace), static_cast<cudaStream_t>(stream));
+  if (rc) return rc;
+  const int64_t n4 = int64_t(args->M) * args->N / 4;
+  int blocks = int((n4 + 255) / 256);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  splitk_reduce_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const float*>(workspace), static_cast<__nv_bfloat16*>(args->C), args->ldc, args->M, args->N, splits,
+      args->alpha);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return set_error(-6, std::string("splitk reduce launch: ") + cudaGetErrorString(e));
+  return 0;
+}
