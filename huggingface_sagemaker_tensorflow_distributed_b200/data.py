@@ -1,0 +1,181 @@
+"""Data pipeline.
+
+The reference tokenises IMDB with the model's tokenizer, pads every example to
+``tokenizer.model_max_length`` (512) and batches without shuffle / shard / repeat
+(scripts/train.py:68-100).  There is no network, dataset cache or vocabulary on this image,
+so the default source is a deterministic **synthetic IMDB-shaped** set: 25 000 train /
+25 000 test examples, binary labels, review-like length distribution, padded to the maximum
+sequence length, feeding only ``input_ids`` and ``attention_mask``.  A small planted signal
+(label-dependent token frequencies) makes the loss curve meaningful.  When
+``SM_CHANNEL_TRAIN`` / ``SM_CHANNEL_TEST`` point at pre-tokenised ``.npz``/``.pt`` files or
+``.jsonl`` text plus a loadable tokenizer, those are used instead.
+
+Sharding: by default rank r takes samples r, r+W, ... (DistributedSampler semantics) so the
+job consumes each example once; ``no_shard=True`` restores the reference behaviour where
+every rank iterates the full set.
+"""
+from __future__ import annotations
+
+import glob
+import json
+import os
+from dataclasses import dataclass
+from typing import Dict, Iterator, Optional, Tuple
+
+import numpy as np
+import torch
+
+from .models.configuration import EncoderConfig
+
+IGNORE_LABEL = -1  # padding rows of a short final batch
+
+
+@dataclass
+class TokenizedDataset:
+    input_ids: np.ndarray  # [N, S] int32
+    attention_mask: np.ndarray  # [N, S] int32 (1 = token, 0 = pad)
+    labels: np.ndarray  # [N] int32
+    source: str = "synthetic"
+
+    def __len__(self) -> int:
+        return int(self.labels.shape[0])
+
+    @property
+    def seq_len(self) -> int:
+        return int(self.input_ids.shape[1])
+
+
+def synthetic_imdb(cfg: EncoderConfig, num_samples: int, seq_len: int, seed: int = 0,
+                   split: str = "train") -> TokenizedDataset:
+    """IMDB-shaped synthetic token data.  Lengths follow a log-normal fitted to IMDB
+    word-piece counts (median ≈ 230, long tail truncated at ``seq_len``)."""
+    rng = np.random.default_rng(seed + (0 if split == "train" else 7919))
+    lengths = np.clip(rng.lognormal(mean=5.45, sigma=0.62, size=num_samples).astype(np.int64), 16, seq_len)
+    labels = rng.integers(0, 2, size=num_samples, dtype=np.int64)
+    special = 4 if cfg.model_type == "roberta" else 1000  # keep clear of [PAD]/[CLS]/[SEP]/unused ids
+    lo = min(special, cfg.vocab_size // 2)
+    ids = rng.integers(lo, cfg.vocab_size, size=(num_samples, seq_len), dtype=np.int64)
+    # planted sentiment: ~6% of tokens come from a label-specific 64-token lexicon
+    lex = lo + np.arange(128) % max(1, cfg.vocab_size - lo)
+    plant = rng.random((num_samples, seq_len)) < 0.06
+    which = rng.integers(0, 64, size=(num_samples, seq_len))
+    planted = lex[(which + 64 * labels[:, None]) % 128]
+    ids = np.where(plant, planted, ids)
+    pos = np.arange(seq_len)[None, :]
+    mask = (pos < lengths[:, None]).astype(np.int32)
+    cls_id, sep_id = (0, 2) if cfg.model_type == "roberta" else (min(101, cfg.vocab_size - 2), min(102, cfg.vocab_size - 1))
+    ids[:, 0] = cls_id
+    ids[np.arange(num_samples), lengths - 1] = sep_id
+    ids = np.where(mask == 1, ids, cfg.pad_token_id).astype(np.int32)
+    return TokenizedDataset(ids, mask, labels.astype(np.int32), source="synthetic")
+
+
+def _pad_to(a: np.ndarray, seq_len: int, value: int) -> np.ndarray:
+    if a.shape[1] == seq_len:
+        return a
+    if a.shape[1] > seq_len:
+        return a[:, :seq_len]
+    out = np.full((a.shape[0], seq_len), value, dtype=a.dtype)
+    out[:, :a.shape[1]] = a
+    return out
+
+
+def load_channel(path: str, cfg: EncoderConfig, seq_len: int, tokenizer=None) -> Optional[TokenizedDataset]:
+    """Reads a SageMaker input channel directory: ``*.npz`` / ``*.pt`` with input_ids,
+    attention_mask, label(s); or ``*.jsonl`` with text + label (needs a tokenizer)."""
+    if not path or not os.path.isdir(path):
+        return None
+    for f in sorted(glob.glob(os.path.join(path, "*.npz"))):
+        z = np.load(f)
+        lab = z["labels"] if "labels" in z else z["label"]
+        return TokenizedDataset(_pad_to(z["input_ids"].astype(np.int32), seq_len, cfg.pad_token_id),
+                                _pad_to(z["attention_mask"].astype(np.int32), seq_len, 0), lab.astype(np.int32), f)
+    for f in sorted(glob.glob(os.path.join(path, "*.pt"))):
+        z = torch.load(f, map_location="cpu", weights_only=True)
+        lab = z["labels"] if "labels" in z else z["label"]
+        return TokenizedDataset(_pad_to(z["input_ids"].numpy().astype(np.int32), seq_len, cfg.pad_token_id),
+                                _pad_to(z["attention_mask"].numpy().astype(np.int32), seq_len, 0),
+                                lab.numpy().astype(np.int32), f)
+    files = sorted(glob.glob(os.path.join(path, "*.jsonl")))
+    if files and tokenizer is not None:
+        texts, labels = [], []
+        for f in files:
+            with open(f) as fh:
+                for line in fh:
+                    if line.strip():
+                        r = json.loads(line)
+                        texts.append(r["text"])
+                        labels.append(int(r["label"]))
+        enc = tokenizer(texts, truncation=True, padding="max_length", max_length=seq_len)
+        return TokenizedDataset(np.asarray(enc["input_ids"], dtype=np.int32),
+                                np.asarray(enc["attention_mask"], dtype=np.int32),
+                                np.asarray(labels, dtype=np.int32), files[0])
+    return None
+
+
+def try_load_tokenizer(name_or_path: Optional[str]):
+    """The model's tokenizer if its files are available locally; else None (synthetic ids)."""
+    if not name_or_path or not os.path.isdir(name_or_path):
+        return None
+    try:
+        from transformers import AutoTokenizer
+
+        return AutoTokenizer.from_pretrained(name_or_path, local_files_only=True)
+    except Exception:  # noqa: BLE001 - no vocab on disk is the common case here
+        return None
+
+
+class BatchedDataset:
+    """``tf.data.Dataset.from_tensor_slices(...).batch(bs)`` stand-in: a re-iterable of
+    ``(features, labels)`` batches with static shapes.  A short final batch is padded with
+    rows whose label is ``IGNORE_LABEL`` (they contribute to neither loss nor accuracy), so
+    kernels and CUDA graphs see one shape."""
+
+    def __init__(self, ds: TokenizedDataset, batch_size: int, rank: int = 0, world_size: int = 1,
+                 shard: bool = True, max_batches: int = -1, pin_memory: bool = False):
+        self.ds, self.batch_size = ds, int(batch_size)
+        idx = np.arange(len(ds))
+        if shard and world_size > 1:
+            idx = idx[rank::world_size]
+        self.indices = idx
+        self.max_batches = max_batches
+        self.pin_memory = pin_memory and torch.cuda.is_available()
+
+    def __len__(self) -> int:
+        n = (len(self.indices) + self.batch_size - 1) // self.batch_size
+        return n if self.max_batches < 0 else min(n, self.max_batches)
+
+    @property
+    def num_samples(self) -> int:
+        return min(len(self.indices), len(self) * self.batch_size)
+
+    def __iter__(self) -> Iterator[Tuple[Dict[str, torch.Tensor], torch.Tensor]]:
+        bs, S = self.batch_size, self.ds.seq_len
+        for b in range(len(self)):
+            sel = self.indices[b * bs:(b + 1) * bs]
+            ids = np.full((bs, S), 0, dtype=np.int32)
+            mask = np.zeros((bs, S), dtype=np.int32)
+            lab = np.full((bs,), IGNORE_LABEL, dtype=np.int32)
+            ids[:len(sel)] = self.ds.input_ids[sel]
+            mask[:len(sel)] = self.ds.attention_mask[sel]
+            lab[:len(sel)] = self.ds.labels[sel]
+            if len(sel) < bs:  # keep padded rows well-formed: one real token
+                mask[len(sel):, 0] = 1
+            feats = {"input_ids": torch.from_numpy(ids), "attention_mask": torch.from_numpy(mask)}
+            labels = torch.from_numpy(lab)
+            if self.pin_memory:
+                feats = {k: v.pin_memory() for k, v in feats.items()}
+                labels = labels.pin_memory()
+            yield feats, labels
+
+
+def build_datasets(cfg: EncoderConfig, *, train_samples: int, test_samples: int, seq_len: int, seed: int,
+                   train_channel: Optional[str] = None, test_channel: Optional[str] = None,
+                   tokenizer=None) -> Tuple[TokenizedDataset, TokenizedDataset]:
+    train = load_channel(train_channel, cfg, seq_len, tokenizer) if train_channel else None
+    test = load_channel(test_channel, cfg, seq_len, tokenizer) if test_channel else None
+    if train is None:
+        train = synthetic_imdb(cfg, train_samples, seq_len, seed, "train")
+    if test is None:
+        test = synthetic_imdb(cfg, test_samples, seq_len, seed, "test")
+    return train, test
