@@ -1,0 +1,195 @@
+// Classification head + sparse softmax cross-entropy + accuracy, forward and backward
+// (reference scripts/train.py:117-119: the HF seq-cls head, Keras
+// SparseCategoricalCrossentropy(from_logits=True) and SparseCategoricalAccuracy).
+// Batch x hidden here is tiny (8 x 768), so these are CUDA-core kernels; the only goal is
+// to keep the whole head in a handful of launches with no host round trip.
+#include "common.cuh"
+#include "device_utils.cuh"
+
+namespace hstd {
+
+__device__ __forceinline__ float head_act(int kind, float z) { return kind == 0 ? fmaxf(z, 0.f) : tanhf(z); }
+// derivative expressed through the stored activation output h
+__device__ __forceinline__ float head_act_grad(int kind, float h) { return kind == 0 ? (h > 0.f ? 1.f : 0.f) : 1.f - h * h; }
+
+__device__ __forceinline__ float drop_mult(const Dropout& d, uint64_t idx) {
+  if (!d.active()) return 1.f;
+  float m[8];
+  dropout_mask8(d, idx >> 3, m);
+  return m[idx & 7];
+}
+
+// h[b,j] = act(b1[j] + sum_k W1[j,k] * drop0(x[b*S, k]));  one warp per (b, j)
+__global__ void __launch_bounds__(256) head_dense_fwd_kernel(const hstd_head_args p) {
+  const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (gw >= p.B * p.d) return;
+  const int b = gw / p.d, j = gw - b * p.d;
+  const Dropout d0 = make_dropout(p.train ? p.state : nullptr, p.kind == 2 ? p.p_drop : 0.f, p.site0);
+  const __nv_bfloat16* x = static_cast<const __nv_bfloat16*>(p.x) + int64_t(b) * p.S * p.d;
+  const __nv_bfloat16* w = static_cast<const __nv_bfloat16*>(p.w1) + int64_t(j) * p.d;
+  float acc = 0.f;
+  for (int k = lane * 8; k < p.d; k += 256) {
+    float xv[8], wv[8];
+    load8(x + k, xv);
+    load8(w + k, wv);
+    if (d0.active()) {
+      float m[8];
+      dropout_mask8(d0, (uint64_t(b) * p.d + k) >> 3, m);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) xv[i] *= m[i];
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc += xv[i] * wv[i];
+  }
+  acc = warp_sum(acc);
+  if (lane == 0)
+    p.h[gw] = head_act(p.kind, acc + __bfloat162float(static_cast<const __nv_bfloat16*>(p.b1)[j]));
+}
+
+// logits, loss, accuracy, dlogits.  Single block; warp w handles samples w, w+nwarps, ...
+__global__ void __launch_bounds__(1024) head_logits_loss_kernel(const hstd_head_args p) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  const Dropout d1 = make_dropout(p.train ? p.state : nullptr, p.p_drop, p.site1);
+  extern __shared__ float sm[];  // [B] loss, [B] correct, [B] valid
+  float* s_loss = sm;
+  float* s_corr = sm + p.B;
+  float* s_valid = sm + 2 * p.B;
+  const __nv_bfloat16* w2 = static_cast<const __nv_bfloat16*>(p.w2);
+  const __nv_bfloat16* b2 = static_cast<const __nv_bfloat16*>(p.b2);
+  for (int b = warp; b < p.B; b += nwarps) {
+    for (int c = 0; c < p.C; ++c) {
+      float acc = 0.f;
+      for (int j = lane; j < p.d; j += 32)
+        acc += p.h[b * p.d + j] * drop_mult(d1, uint64_t(b) * p.d + j) * __bfloat162float(w2[int64_t(c) * p.d + j]);
+      acc = warp_sum(acc);
+      if (lane == 0) p.logits[b * p.C + c] = acc + __bfloat162float(b2[c]);
+    }
+    __syncwarp();
+    if (lane == 0) {
+      const int label = p.labels[b];
+      float mx = -INFINITY;
+      int arg = 0;
+      for (int c = 0; c < p.C; ++c) {
+        const float l = p.logits[b * p.C + c];
+        if (l > mx) { mx = l; arg = c; }
+      }
+      float se = 0.f;
+      for (int c = 0; c < p.C; ++c) se += expf(p.logits[b * p.C + c] - mx);
+      const float lse = mx + logf(se);
+      const bool valid = label >= 0 && label < p.C;
+      s_valid[b] = valid ? 1.f : 0.f;
+      s_loss[b] = valid ? lse - p.logits[b * p.C + label] : 0.f;
+      s_corr[b] = (valid && arg == label) ? 1.f : 0.f;
+    }
+  }
+  __syncthreads();
+  __shared__ float s_count;
+  if (threadIdx.x == 0) {
+    float ls = 0.f, cs = 0.f, n = 0.f;
+    for (int b = 0; b < p.B; ++b) { ls += s_loss[b]; cs += s_corr[b]; n += s_valid[b]; }
+    s_count = n;
+    p.state->metrics[0] = ls; p.state->metrics[1] = cs; p.state->metrics[2] = n;
+    p.state->metrics_acc[0] += ls; p.state->metrics_acc[1] += cs; p.state->metrics_acc[2] += n;
+  }
+  __syncthreads();
+  if (p.dlogits != nullptr) {
+    const float inv = s_count > 0.f ? 1.f / s_count : 0.f;
+    for (int i = threadIdx.x; i < p.B * p.C; i += blockDim.x) {
+      const int b = i / p.C, c = i - b * p.C;
+      const int label = p.labels[b];
+      float g = 0.f;
+      if (s_valid[b] > 0.f) {
+        float mx = -INFINITY;
+        for (int k = 0; k < p.C; ++k) mx = fmaxf(mx, p.logits[b * p.C + k]);
+        float se = 0.f;
+        for (int k = 0; k < p.C; ++k) se += expf(p.logits[b * p.C + k] - mx);
+        g = (expf(p.logits[i] - mx) / se - (c == label ? 1.f : 0.f)) * inv;
+      }
+      p.dlogits[i] = g;
+    }
+  }
+}
+
+// thread per hidden column j: dz[b,j] for all b, dW2[c,j] for all c; thread 0.. also db2.
+__global__ void __launch_bounds__(256) head_bwd_dz_kernel(const hstd_head_args p) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  const Dropout d1 = make_dropout(p.state, p.p_drop, p.site1);
+  const __nv_bfloat16* w2 = static_cast<const __nv_bfloat16*>(p.w2);
+  if (j < p.d) {
+    for (int c = 0; c < p.C; ++c) {
+      float acc = 0.f;
+      for (int b = 0; b < p.B; ++b)
+        acc += p.dlogits[b * p.C + c] * p.h[b * p.d + j] * drop_mult(d1, uint64_t(b) * p.d + j);
+      static_cast<__nv_bfloat16*>(p.dw2)[int64_t(c) * p.d + j] = __float2bfloat16_rn(acc);
+    }
+    for (int b = 0; b < p.B; ++b) {
+      float dh = 0.f;
+      for (int c = 0; c < p.C; ++c) dh += p.dlogits[b * p.C + c] * __bfloat162float(w2[int64_t(c) * p.d + j]);
+      const float h = p.h[b * p.d + j];
+      p.dz[b * p.d + j] = dh * drop_mult(d1, uint64_t(b) * p.d + j) * head_act_grad(p.kind, h);
+    }
+  }
+  if (j < p.C) {
+    float acc = 0.f;
+    for (int b = 0; b < p.B; ++b) acc += p.dlogits[b * p.C + j];
+    static_cast<__nv_bfloat16*>(p.db2)[j] = __float2bfloat16_rn(acc);
+  }
+}
+
+// dW1[j,k] = sum_b dz[b,j] * drop0(x[b,k]);  db1[j] = sum_b dz[b,j].  grid (d/256, d)
+__global__ void __launch_bounds__(256) head_bwd_dw1_kernel(const hstd_head_args p) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y;
+  if (k >= p.d) return;
+  const Dropout d0 = make_dropout(p.state, p.kind == 2 ? p.p_drop : 0.f, p.site0);
+  const __nv_bfloat16* x = static_cast<const __nv_bfloat16*>(p.x);
+  float acc = 0.f, accb = 0.f;
+  for (int b = 0; b < p.B; ++b) {
+    const float dz = p.dz[b * p.d + j];
+    acc += dz * __bfloat162float(x[int64_t(b) * p.S * p.d + k]) * drop_mult(d0, uint64_t(b) * p.d + k);
+    accb += dz;
+  }
+  static_cast<__nv_bfloat16*>(p.dw1)[int64_t(j) * p.d + k] = __float2bfloat16_rn(acc);
+  if (k == 0) static_cast<__nv_bfloat16*>(p.db1)[j] = __float2bfloat16_rn(accb);
+}
+
+// dx[b*S, k] = drop0'( sum_j dz[b,j] * W1[j,k] ).  thread per (b,k)
+__global__ void __launch_bounds__(256) head_bwd_dx_kernel(const hstd_head_args p) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= p.B * p.d) return;
+  const int b = i / p.d, k = i - b * p.d;
+  const Dropout d0 = make_dropout(p.state, p.kind == 2 ? p.p_drop : 0.f, p.site0);
+  const __nv_bfloat16* w1 = static_cast<const __nv_bfloat16*>(p.w1);
+  float acc = 0.f;
+  for (int j = 0; j < p.d; ++j) acc += p.dz[b * p.d + j] * __bfloat162float(w1[int64_t(j) * p.d + k]);
+  acc *= drop_mult(d0, uint64_t(b) * p.d + k);
+  static_cast<__nv_bfloat16*>(p.dx)[int64_t(b) * p.S * p.d + k] = __float2bfloat16_rn(acc);
+}
+
+}  // namespace hstd
+
+using namespace hstd;
+
+extern "C" HSTD_API int hstd_head_fwd(const hstd_head_args* a, void* stream) {
+  if (a->d % 8 != 0) return set_error(-1, "head: d must be a multiple of 8");
+  if (a->B > 2048) return set_error(-1, "head: batch too large");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int64_t threads = int64_t(a->B) * a->d * 32;
+  head_dense_fwd_kernel<<<unsigned((threads + 255) / 256), 256, 0, s>>>(*a);
+  if (int rc = check_launch("head_dense_fwd")) return rc;
+  head_logits_loss_kernel<<<1, 1024, 3 * a->B * sizeof(float), s>>>(*a);
+  return check_launch("head_logits_loss");
+}
+
+extern "C" HSTD_API int hstd_head_bwd(const hstd_head_args* a, void* stream) {
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (!a->dlogits || !a->dz || !a->dx) return set_error(-1, "head_bwd: dlogits, dz and dx are required");
+  cudaError_t e = cudaMemsetAsync(a->dx, 0, size_t(a->B) * a->S * a->d * 2, s);
+  if (e != cudaSuccess) return set_error(-6, std::string("head_bwd memset: ") + cudaGetErrorString(e));
+  const int cols = a->d > a->C ? a->d : a->C;
+  head_bwd_dz_kernel<<<(cols + 255) / 256, 256, 0, s>>>(*a);
+  if (int rc = check_launch("head_bwd_dz")) return rc;
+  head_bwd_dw1_kernel<<<dim3((a->d + 255) / 256, a->d), 256, 0, s>>>(*a);
+  if (int rc = check_launch("head_bwd_dw1")) return rc;
+  head_bwd_dx_kernel<<<(a->B * a->d + 255) / 256, 256, 0, s>>>(*a);
+  return check_launch("head_bwd_dx");
+}

@@ -1,0 +1,475 @@
+// Memory-bound row kernels: fused (embedding gather | dropout + residual) + LayerNorm
+// forward/backward, bias-gradient column sums, masked attention softmax (+dropout)
+// forward/backward, embedding scatter-add and position ids.
+//
+// One warp owns one row; every lane moves 16-byte vectors, statistics are warp-shuffle
+// reductions in fp32, dropout masks are regenerated from a Philox counter in backward.
+// These replace the TF primitive chains the reference runs for LayerNorm / softmax /
+// dropout / gather inside model.fit (scripts/train.py:145).
+#include <cub/block/block_scan.cuh>
+
+#include "common.cuh"
+#include "device_utils.cuh"
+
+namespace hstd {
+
+constexpr int LN_WARPS = 8;
+constexpr int LN_BWD_MAX_BLOCKS = 296;  // 2 per SM
+
+// ------------------------------------------------------------------ LayerNorm forward
+template <int NV, bool EMBED>
+__global__ void __launch_bounds__(LN_WARPS * 32) ln_fwd_kernel(const hstd_ln_args p) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * LN_WARPS + warp;
+  if (row >= p.M) return;
+  const int d = p.d;
+  const Dropout din = make_dropout(p.state, p.p_in, p.site_in);
+  const Dropout dout = make_dropout(p.state, p.p_out, p.site_out);
+  const __nv_bfloat16* gamma = static_cast<const __nv_bfloat16*>(p.gamma);
+  const __nv_bfloat16* beta = static_cast<const __nv_bfloat16*>(p.beta);
+
+  float v[NV][8];
+  float sum = 0.f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int col = i * 256 + lane * 8;
+    if constexpr (EMBED) {
+      const int id = p.ids[row], pid = p.pos_ids[row];
+      float w[8], q[8];
+      load8(static_cast<const __nv_bfloat16*>(p.word) + int64_t(id) * d + col, w);
+      load8(static_cast<const __nv_bfloat16*>(p.pos) + int64_t(pid) * d + col, q);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[i][j] = w[j] + q[j];
+      if (p.type0) {
+        load8(static_cast<const __nv_bfloat16*>(p.type0) + col, q);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[i][j] += q[j];
+      }
+    } else {
+      load8(static_cast<const __nv_bfloat16*>(p.a) + int64_t(row) * d + col, v[i]);
+      if (din.active()) {
+        float m[8];
+        dropout_mask8(din, (uint64_t(row) * d + col) >> 3, m);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[i][j] *= m[j];
+      }
+      if (p.resid) {
+        float r[8];
+        load8(static_cast<const __nv_bfloat16*>(p.resid) + int64_t(row) * d + col, r);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[i][j] += r[j];
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      v[i][j] = bf16_round(v[i][j]);
+      sum += v[i][j];
+    }
+    if (p.pre) store8(static_cast<__nv_bfloat16*>(p.pre) + int64_t(row) * d + col, v[i]);
+  }
+  const float mean = warp_sum(sum) / float(d);
+  float sq = 0.f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float c = v[i][j] - mean;
+      sq += c * c;
+    }
+  const float rstd = rsqrtf(warp_sum(sq) / float(d) + p.eps);
+  if (lane == 0) {
+    if (p.mean) p.mean[row] = mean;
+    if (p.rstd) p.rstd[row] = rstd;
+  }
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int col = i * 256 + lane * 8;
+    float g[8], b[8], o[8];
+    load8(gamma + col, g);
+    load8(beta + col, b);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = (v[i][j] - mean) * rstd * g[j] + b[j];
+    if (dout.active()) {
+      float m[8];
+      dropout_mask8(dout, (uint64_t(row) * d + col) >> 3, m);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] *= m[j];
+    }
+    store8(static_cast<__nv_bfloat16*>(p.y) + int64_t(row) * d + col, o);
+  }
+}
+
+// ------------------------------------------------------------------ LayerNorm backward
+// partials layout: [gridDim.x][3][d] floats (dgamma, dbeta, dbias)
+template <int NV>
+__global__ void __launch_bounds__(LN_WARPS * 32) ln_bwd_kernel(const hstd_ln_bwd_args p) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int d = p.d;
+  const Dropout din = make_dropout(p.state, p.p_in, p.site_in);
+  const Dropout dout = make_dropout(p.state, p.p_out, p.site_out);
+  const __nv_bfloat16* gamma = static_cast<const __nv_bfloat16*>(p.gamma);
+  float g[NV][8];
+#pragma unroll
+  for (int i = 0; i < NV; ++i) load8(gamma + i * 256 + lane * 8, g[i]);
+  float acc_g[NV][8], acc_b[NV][8], acc_a[NV][8];
+#pragma unroll
+  for (int i = 0; i < NV; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc_g[i][j] = acc_b[i][j] = acc_a[i][j] = 0.f;
+
+  for (int row = blockIdx.x * LN_WARPS + warp; row < p.M; row += gridDim.x * LN_WARPS) {
+    const float mean = p.mean[row], rstd = p.rstd[row];
+    float dy[NV][8], xh[NV][8];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int col = i * 256 + lane * 8;
+      load8(static_cast<const __nv_bfloat16*>(p.dy) + int64_t(row) * d + col, dy[i]);
+      if (dout.active()) {
+        float m[8];
+        dropout_mask8(dout, (uint64_t(row) * d + col) >> 3, m);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) dy[i][j] *= m[j];
+      }
+      load8(static_cast<const __nv_bfloat16*>(p.pre) + int64_t(row) * d + col, xh[i]);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        xh[i][j] = (xh[i][j] - mean) * rstd;
+        const float gd = g[i][j] * dy[i][j];
+        s1 += gd;
+        s2 += gd * xh[i][j];
+        acc_g[i][j] += dy[i][j] * xh[i][j];
+        acc_b[i][j] += dy[i][j];
+      }
+    }
+    s1 = warp_sum(s1) / float(d);
+    s2 = warp_sum(s2) / float(d);
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int col = i * 256 + lane * 8;
+      float dp[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) dp[j] = rstd * (g[i][j] * dy[i][j] - s1 - xh[i][j] * s2);
+      store8(static_cast<__nv_bfloat16*>(p.dpre) + int64_t(row) * d + col, dp);
+      if (p.da != nullptr) {
+        if (din.active()) {
+          float m[8];
+          dropout_mask8(din, (uint64_t(row) * d + col) >> 3, m);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) dp[j] *= m[j];
+        }
+        store8(static_cast<__nv_bfloat16*>(p.da) + int64_t(row) * d + col, dp);
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc_a[i][j] += bf16_round(dp[j]);
+    }
+  }
+
+  // block reduction over the LN_WARPS warps, one quantity at a time through smem
+  __shared__ float red[LN_WARPS][NV * 256];
+  float* out = p.partials + int64_t(blockIdx.x) * 3 * d;
+#pragma unroll
+  for (int q = 0; q < 3; ++q) {
+#pragma unroll
+    for (int i = 0; i < NV; ++i)
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        red[warp][i * 256 + lane * 8 + j] = (q == 0 ? acc_g[i][j] : (q == 1 ? acc_b[i][j] : acc_a[i][j]));
+    __syncthreads();
+    for (int c = threadIdx.x; c < d; c += LN_WARPS * 32) {
+      float s = 0.f;
+#pragma unroll
+      for (int w = 0; w < LN_WARPS; ++w) s += red[w][c];
+      out[q * d + c] = s;
+    }
+    __syncthreads();
+  }
+}
+
+// Sum `nparts` partial rows of `width` floats and scatter segments of `seg` columns to up
+// to three bf16 destinations (dst[k] may be null).
+__global__ void partials_finalize_kernel(const float* __restrict__ partials, int nparts, int width, int seg,
+                                         __nv_bfloat16* d0, __nv_bfloat16* d1, __nv_bfloat16* d2) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= width) return;
+  float s = 0.f;
+  for (int i = 0; i < nparts; ++i) s += partials[int64_t(i) * width + c];
+  const int k = c / seg;
+  __nv_bfloat16* dst = k == 0 ? d0 : (k == 1 ? d1 : d2);
+  if (dst) dst[c - k * seg] = __float2bfloat16_rn(s);
+}
+
+// ------------------------------------------------------------------ column sums
+constexpr int COLSUM_ROWGROUPS = 32;
+__global__ void __launch_bounds__(256) colsum_partial_kernel(const __nv_bfloat16* __restrict__ x, int64_t ld, int M,
+                                                             int N, float* __restrict__ partials) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int col = blockIdx.x * 256 + lane * 8;
+  float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  if (col < N) {
+    for (int row = blockIdx.y * 8 + warp; row < M; row += gridDim.y * 8) {
+      float v[8];
+      load8(x + int64_t(row) * ld + col, v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += v[j];
+    }
+  }
+  __shared__ float red[8][256];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) red[warp][lane * 8 + j] = acc[j];
+  __syncthreads();
+  const int c = threadIdx.x;
+  if (blockIdx.x * 256 + c < N) {
+    float s = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) s += red[w][c];
+    partials[int64_t(blockIdx.y) * N + blockIdx.x * 256 + c] = s;
+  }
+}
+
+// ------------------------------------------------------------------ softmax
+// NV4 = Sk / 128; lane handles 4 contiguous keys at (i*32 + lane)*4.
+template <int NV4>
+__global__ void __launch_bounds__(256) softmax_fwd_kernel(__nv_bfloat16* __restrict__ sp, __nv_bfloat16* __restrict__ pd,
+                                                          const int32_t* __restrict__ key_mask, int rows, int H, int Sq,
+                                                          float p_drop, uint32_t site, const StepState* st) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t row = int64_t(blockIdx.x) * 8 + warp;
+  if (row >= rows) return;
+  constexpr int Sk = NV4 * 128;
+  const int b = int(row / (int64_t(H) * Sq));
+  const Dropout dr = make_dropout(st, p_drop, site);
+  __nv_bfloat16* src = sp + row * Sk;
+  float v[NV4][4];
+  float mx = -INFINITY;
+#pragma unroll
+  for (int i = 0; i < NV4; ++i) {
+    const int col = (i * 32 + lane) * 4;
+    const uint2 u = *reinterpret_cast<const uint2*>(src + col);
+    const int4 km = *reinterpret_cast<const int4*>(key_mask + int64_t(b) * Sk + col);
+    const float2 a = unpack_bf16x2_dev(u.x), c = unpack_bf16x2_dev(u.y);
+    v[i][0] = km.x ? a.x : -INFINITY;
+    v[i][1] = km.y ? a.y : -INFINITY;
+    v[i][2] = km.z ? c.x : -INFINITY;
+    v[i][3] = km.w ? c.y : -INFINITY;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) mx = fmaxf(mx, v[i][j]);
+  }
+  mx = warp_max(mx);
+  if (mx == -INFINITY) mx = 0.f;  // fully masked row: all probabilities become 0
+  float sum = 0.f;
+#pragma unroll
+  for (int i = 0; i < NV4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      v[i][j] = __expf(v[i][j] - mx);
+      sum += v[i][j];
+    }
+  sum = warp_sum(sum);
+  const float inv = sum > 0.f ? 1.f / sum : 0.f;
+#pragma unroll
+  for (int i = 0; i < NV4; ++i) {
+    const int col = (i * 32 + lane) * 4;
+    float pr[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) pr[j] = v[i][j] * inv;
+    uint2 o;
+    o.x = pack_bf16x2_dev(pr[0], pr[1]);
+    o.y = pack_bf16x2_dev(pr[2], pr[3]);
+    *reinterpret_cast<uint2*>(src + col) = o;
+    if (pd != nullptr) {
+      if (dr.active()) {
+        // one Philox call covers 8 elements: lanes pair up on the same group
+        float m[8];
+        const uint64_t e = uint64_t(row) * Sk + col;
+        dropout_mask8(dr, e >> 3, m);
+        const int h = (e & 4) ? 4 : 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) pr[j] *= m[h + j];
+      }
+      o.x = pack_bf16x2_dev(pr[0], pr[1]);
+      o.y = pack_bf16x2_dev(pr[2], pr[3]);
+      *reinterpret_cast<uint2*>(pd + row * Sk + col) = o;
+    }
+  }
+}
+
+template <int NV4>
+__global__ void __launch_bounds__(256) softmax_bwd_kernel(const __nv_bfloat16* __restrict__ P,
+                                                          __nv_bfloat16* __restrict__ dpd, int rows, float p_drop,
+                                                          uint32_t site, const StepState* st) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t row = int64_t(blockIdx.x) * 8 + warp;
+  if (row >= rows) return;
+  constexpr int Sk = NV4 * 128;
+  const Dropout dr = make_dropout(st, p_drop, site);
+  float pr[NV4][4], dp[NV4][4];
+  float dot = 0.f;
+#pragma unroll
+  for (int i = 0; i < NV4; ++i) {
+    const int col = (i * 32 + lane) * 4;
+    const uint2 up = *reinterpret_cast<const uint2*>(P + row * Sk + col);
+    const uint2 ud = *reinterpret_cast<const uint2*>(dpd + row * Sk + col);
+    float2 a = unpack_bf16x2_dev(up.x), c = unpack_bf16x2_dev(up.y);
+    pr[i][0] = a.x; pr[i][1] = a.y; pr[i][2] = c.x; pr[i][3] = c.y;
+    a = unpack_bf16x2_dev(ud.x); c = unpack_bf16x2_dev(ud.y);
+    dp[i][0] = a.x; dp[i][1] = a.y; dp[i][2] = c.x; dp[i][3] = c.y;
+    if (dr.active()) {
+      float m[8];
+      const uint64_t e = uint64_t(row) * Sk + col;
+      dropout_mask8(dr, e >> 3, m);
+      const int h = (e & 4) ? 4 : 0;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) dp[i][j] *= m[h + j];
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) dot += dp[i][j] * pr[i][j];
+  }
+  dot = warp_sum(dot);
+#pragma unroll
+  for (int i = 0; i < NV4; ++i) {
+    const int col = (i * 32 + lane) * 4;
+    uint2 o;
+    o.x = pack_bf16x2_dev(pr[i][0] * (dp[i][0] - dot), pr[i][1] * (dp[i][1] - dot));
+    o.y = pack_bf16x2_dev(pr[i][2] * (dp[i][2] - dot), pr[i][3] * (dp[i][3] - dot));
+    *reinterpret_cast<uint2*>(dpd + row * Sk + col) = o;
+  }
+}
+
+// ------------------------------------------------------------------ embeddings
+__global__ void position_ids_kernel(const int32_t* __restrict__ ids, int32_t* __restrict__ pos, int S, int mode,
+                                    int pad_id) {
+  using Scan = cub::BlockScan<int, 1024>;
+  __shared__ typename Scan::TempStorage tmp;
+  const int b = blockIdx.x, s = threadIdx.x;
+  int nonpad = 0;
+  if (s < S) nonpad = (ids[int64_t(b) * S + s] != pad_id) ? 1 : 0;
+  int incl;
+  Scan(tmp).InclusiveSum(nonpad, incl);
+  if (s < S) pos[int64_t(b) * S + s] = mode == 0 ? s : incl * nonpad + pad_id;
+}
+
+template <int NV>
+__global__ void __launch_bounds__(256) embed_bwd_kernel(const __nv_bfloat16* __restrict__ de,
+                                                        const int32_t* __restrict__ ids,
+                                                        const int32_t* __restrict__ pos_ids,
+                                                        __nv_bfloat16* __restrict__ word_grad,
+                                                        __nv_bfloat16* __restrict__ pos_grad, int M, int d) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * 8 + warp;
+  if (row >= M) return;
+  const int id = ids[row], pid = pos_ids[row];
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int col = i * 256 + lane * 8;
+    const uint4 u = *reinterpret_cast<const uint4*>(de + int64_t(row) * d + col);
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+    __nv_bfloat162* w = reinterpret_cast<__nv_bfloat162*>(word_grad + int64_t(id) * d + col);
+    __nv_bfloat162* q = reinterpret_cast<__nv_bfloat162*>(pos_grad + int64_t(pid) * d + col);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      atomicAdd(w + j, h[j]);
+      atomicAdd(q + j, h[j]);
+    }
+  }
+}
+
+static int check_d(int d, const char* who) {
+  if (d % 256 != 0 || d < 256 || d > 1024)
+    return set_error(-1, std::string(who) + ": hidden size must be a multiple of 256 in [256, 1024]");
+  return 0;
+}
+
+}  // namespace hstd
+
+using namespace hstd;
+
+#define HSTD_DISPATCH_NV(NV_EXPR, ...)         \
+  switch (NV_EXPR) {                           \
+    case 1: { constexpr int NV = 1; __VA_ARGS__; break; } \
+    case 2: { constexpr int NV = 2; __VA_ARGS__; break; } \
+    case 3: { constexpr int NV = 3; __VA_ARGS__; break; } \
+    case 4: { constexpr int NV = 4; __VA_ARGS__; break; } \
+    default: return set_error(-1, "unsupported vector count"); \
+  }
+
+extern "C" HSTD_API int hstd_ln_fwd(const hstd_ln_args* a, void* stream) {
+  if (int rc = check_d(a->d, "ln_fwd")) return rc;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int blocks = (a->M + LN_WARPS - 1) / LN_WARPS;
+  const bool embed = a->ids != nullptr;
+  HSTD_DISPATCH_NV(a->d / 256, if (embed) ln_fwd_kernel<NV, true><<<blocks, LN_WARPS * 32, 0, s>>>(*a);
+                   else ln_fwd_kernel<NV, false><<<blocks, LN_WARPS * 32, 0, s>>>(*a));
+  return check_launch("ln_fwd");
+}
+
+extern "C" HSTD_API int64_t hstd_ln_bwd_partials_floats(int d) { return int64_t(LN_BWD_MAX_BLOCKS) * 3 * d; }
+
+extern "C" HSTD_API int hstd_ln_bwd(const hstd_ln_bwd_args* a, void* stream) {
+  if (int rc = check_d(a->d, "ln_bwd")) return rc;
+  if (!a->partials) return set_error(-1, "ln_bwd: partials scratch is required");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  int blocks = (a->M + LN_WARPS - 1) / LN_WARPS;
+  if (blocks > LN_BWD_MAX_BLOCKS) blocks = LN_BWD_MAX_BLOCKS;
+  HSTD_DISPATCH_NV(a->d / 256, ln_bwd_kernel<NV><<<blocks, LN_WARPS * 32, 0, s>>>(*a));
+  if (int rc = check_launch("ln_bwd")) return rc;
+  const int width = 3 * a->d;
+  partials_finalize_kernel<<<(width + 255) / 256, 256, 0, s>>>(
+      a->partials, blocks, width, a->d, static_cast<__nv_bfloat16*>(a->dgamma), static_cast<__nv_bfloat16*>(a->dbeta),
+      static_cast<__nv_bfloat16*>(a->dbias));
+  return check_launch("ln_bwd finalize");
+}
+
+extern "C" HSTD_API int64_t hstd_colsum_partials_floats(int N) { return int64_t(COLSUM_ROWGROUPS) * N; }
+
+extern "C" HSTD_API int hstd_colsum(const void* x, int64_t ld, int M, int N, void* out, float* partials, void* stream) {
+  if (N % 8 != 0) return set_error(-1, "colsum: N must be a multiple of 8");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  dim3 grid((N + 255) / 256, COLSUM_ROWGROUPS);
+  colsum_partial_kernel<<<grid, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(x), ld, M, N, partials);
+  if (int rc = check_launch("colsum")) return rc;
+  partials_finalize_kernel<<<(N + 255) / 256, 256, 0, s>>>(partials, COLSUM_ROWGROUPS, N, N,
+                                                           static_cast<__nv_bfloat16*>(out), nullptr, nullptr);
+  return check_launch("colsum finalize");
+}
+
+extern "C" HSTD_API int hstd_softmax_fwd(void* sp, void* pd, const int32_t* key_mask, int B, int H, int Sq, int Sk,
+                                         float p_drop, uint32_t site, const hstd_step_state* st, void* stream) {
+  if (Sk % 128 != 0 || Sk > 512) return set_error(-1, "softmax: Sk must be 128, 256, 384 or 512");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int64_t rows = int64_t(B) * H * Sq;
+  const int blocks = int((rows + 7) / 8);
+  HSTD_DISPATCH_NV(Sk / 128, softmax_fwd_kernel<NV><<<blocks, 256, 0, s>>>(
+                                 static_cast<__nv_bfloat16*>(sp), static_cast<__nv_bfloat16*>(pd), key_mask, int(rows), H,
+                                 Sq, p_drop, site, st));
+  return check_launch("softmax_fwd");
+}
+
+extern "C" HSTD_API int hstd_softmax_bwd(const void* p, void* dpd, int B, int H, int Sq, int Sk, float p_drop,
+                                         uint32_t site, const hstd_step_state* st, void* stream) {
+  if (Sk % 128 != 0 || Sk > 512) return set_error(-1, "softmax: Sk must be 128, 256, 384 or 512");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int64_t rows = int64_t(B) * H * Sq;
+  const int blocks = int((rows + 7) / 8);
+  HSTD_DISPATCH_NV(Sk / 128, softmax_bwd_kernel<NV><<<blocks, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(p),
+                                                                           static_cast<__nv_bfloat16*>(dpd), int(rows),
+                                                                           p_drop, site, st));
+  return check_launch("softmax_bwd");
+}
+
+extern "C" HSTD_API int hstd_position_ids(const int32_t* ids, int32_t* pos, int B, int S, int mode, int pad_id,
+                                          void* stream) {
+  if (S > 1024) return set_error(-1, "position_ids: S must be <= 1024");
+  position_ids_kernel<<<B, 1024, 0, static_cast<cudaStream_t>(stream)>>>(ids, pos, S, mode, pad_id);
+  return check_launch("position_ids");
+}
+
+extern "C" HSTD_API int hstd_embed_bwd(const void* de, const int32_t* ids, const int32_t* pos_ids, void* word_grad,
+                                       void* pos_grad, int M, int d, void* stream) {
+  if (int rc = check_d(d, "embed_bwd")) return rc;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  HSTD_DISPATCH_NV(d / 256, embed_bwd_kernel<NV><<<(M + 7) / 8, 256, 0, s>>>(
+                                static_cast<const __nv_bfloat16*>(de), ids, pos_ids,
+                                static_cast<__nv_bfloat16*>(word_grad), static_cast<__nv_bfloat16*>(pos_grad), M, d));
+  return check_launch("embed_bwd");
+}

@@ -74,6 +74,125 @@ int hstd_gemm_bf16_splitk(const hstd_gemm_args* args, int splits, void* workspac
                           void* stream);
 int64_t hstd_gemm_splitk_workspace_bytes(int M, int N, int splits);
 
+/* ------------------------------------------------------------------ per-step device state
+ * Lives in device memory so a captured CUDA graph can be replayed every step: the prologue
+ * kernel advances the step counter, evaluates the LR schedule and the Keras-Adam bias
+ * correction (reference scripts/train.py:112-113: Adam(lr * size), Keras eps placement) and
+ * re-keys the dropout RNG.  `metrics` is {loss_sum, correct, count} of the last step and
+ * `metrics_acc` their running sums since the last hstd_metrics_reset. */
+typedef struct hstd_step_state {
+  int64_t step;  /* optimizer steps taken, including the current one after the prologue */
+  uint64_t seed; /* dropout RNG key */
+  float lr;      /* schedule value for this step */
+  float lr_t;    /* lr * sqrt(1 - b2^t) / (1 - b1^t) */
+  float decay;   /* 1 - lr * weight_decay */
+  float beta1, beta2, eps;
+  float metrics[4];
+  double metrics_acc[4];
+} hstd_step_state;
+
+enum { HSTD_SCHED_CONSTANT = 0, HSTD_SCHED_LINEAR = 1 };
+
+int hstd_step_state_init(hstd_step_state* dev_state, uint64_t seed, int64_t step, void* stream);
+int hstd_step_prologue(hstd_step_state* dev_state, float base_lr, int schedule, int64_t total_steps,
+                       int64_t warmup_steps, float beta1, float beta2, float eps, float weight_decay, void* stream);
+int hstd_metrics_reset(hstd_step_state* dev_state, void* stream);
+
+/* Keras-Adam(W) on a flat parameter arena (K11; reference scripts/train.py:113).  grads are
+ * bf16, master/m/v fp32, the refreshed bf16 weights are written to `w_bf16`.  `grad_scale`
+ * multiplies the gradient first (1/world_size when the sum was formed elsewhere). */
+int hstd_adamw_flat(const hstd_step_state* st, const void* grads_bf16, float* master, float* m, float* v,
+                    void* w_bf16, int64_t n, float grad_scale, void* stream);
+
+/* ------------------------------------------------------------------ LayerNorm family (K1, K4, K6)
+ * Row-wise kernels, hidden size d must be a multiple of 256 and <= 1024.
+ *   forward :  pre = dropout_in(a) + resid ;  y = dropout_out(LN(pre) * gamma + beta)
+ *   embedding forward: a is gathered as word[ids] + pos[pos_ids] (+ type0)
+ * `pre`, `mean`, `rstd` are saved for backward; dropout masks are regenerated from
+ * (state->seed, state->step, site) and never stored.  state==NULL or p==0 disables dropout. */
+typedef struct hstd_ln_args {
+  const void* a;      /* bf16 [M,d] (NULL for the embedding variant) */
+  const void* resid;  /* bf16 [M,d] or NULL */
+  const void* gamma;  /* bf16 [d] */
+  const void* beta;   /* bf16 [d] */
+  void* pre;          /* bf16 [M,d] out (may alias a) */
+  void* y;            /* bf16 [M,d] out */
+  float* mean;        /* [M] out */
+  float* rstd;        /* [M] out */
+  const int32_t* ids; /* embedding variant: [M] token ids */
+  const int32_t* pos_ids;
+  const void* word;   /* bf16 [V,d] */
+  const void* pos;    /* bf16 [P,d] */
+  const void* type0;  /* bf16 [d] or NULL */
+  const hstd_step_state* state;
+  int32_t M, d;
+  float eps, p_in, p_out;
+  uint32_t site_in, site_out;
+} hstd_ln_args;
+int hstd_ln_fwd(const hstd_ln_args* args, void* stream);
+
+/* backward: given dy, recompute xhat from (pre, mean, rstd):
+ *   dpre = LN'(dropout_out'(dy)) ; da = dropout_in'(dpre)  (da may be NULL when p_in == 0)
+ *   dgamma, dbeta, dbias (= column sums of da, or of dpre when da==NULL) reduced over rows.
+ * `partials` is caller scratch of hstd_ln_bwd_partials_floats(d) floats. */
+typedef struct hstd_ln_bwd_args {
+  const void* dy; const void* pre; const float* mean; const float* rstd; const void* gamma;
+  void* dpre; void* da;
+  void* dgamma; void* dbeta; void* dbias; /* bf16 [d] each; dbias may be NULL */
+  float* partials;
+  const hstd_step_state* state;
+  int32_t M, d;
+  float p_in, p_out;
+  uint32_t site_in, site_out;
+} hstd_ln_bwd_args;
+int hstd_ln_bwd(const hstd_ln_bwd_args* args, void* stream);
+int64_t hstd_ln_bwd_partials_floats(int d);
+
+/* Column sums of a bf16 [M,N] matrix into bf16 [N] (bias gradients).  `partials`: scratch
+ * of hstd_colsum_partials_floats(N) floats. */
+int hstd_colsum(const void* x, int64_t ld, int M, int N, void* out_bf16, float* partials, void* stream);
+int64_t hstd_colsum_partials_floats(int N);
+
+/* ------------------------------------------------------------------ attention softmax (K3)
+ * scores: bf16 [B,H,Sq,Sk] (already scaled), key mask int32 [B,Sk] (1 = attend).
+ * forward : P = softmax(scores + mask) written in place; Pd = dropout(P) written to `pd`
+ *           (pd may be NULL when p == 0: use P).
+ * backward: dpd (= dO·Vᵀ) is overwritten with dS = P ∘ (dP − rowsum(dP ∘ P)), dP = dropout'(dpd). */
+int hstd_softmax_fwd(void* scores_p, void* pd, const int32_t* key_mask, int B, int H, int Sq, int Sk, float p_drop,
+                     uint32_t site, const hstd_step_state* st, void* stream);
+int hstd_softmax_bwd(const void* p, void* dpd_ds, int B, int H, int Sq, int Sk, float p_drop, uint32_t site,
+                     const hstd_step_state* st, void* stream);
+
+/* ------------------------------------------------------------------ embeddings (K1)
+ * position ids: mode 0 = arange(S); mode 1 = RoBERTa (cumsum(ids != pad) * (ids != pad) + pad). */
+int hstd_position_ids(const int32_t* ids, int32_t* pos_ids, int B, int S, int mode, int pad_id, void* stream);
+/* scatter-add de [M,d] into word_grad[ids] and pos_grad[pos_ids] (bf16 tables, zeroed by the caller). */
+int hstd_embed_bwd(const void* de, const int32_t* ids, const int32_t* pos_ids, void* word_grad, void* pos_grad,
+                   int M, int d, void* stream);
+
+/* ------------------------------------------------------------------ classification head + loss (K7, K8)
+ * x: bf16 [B*S, d] final hidden states; pooled = row b*S of x.  kind: 0 DistilBERT
+ * (Linear-ReLU-drop-Linear), 1 BERT (Linear-tanh-drop-Linear), 2 RoBERTa
+ * (drop-Linear-tanh-drop-Linear).  labels int32 [B], -1 = ignore.  Loss is the mean over valid
+ * rows of sparse softmax cross-entropy from logits (reference scripts/train.py:118-119).
+ * forward writes logits [B,C] fp32, dlogits (d loss / d logits, already divided by the valid
+ * count), h [B,d] fp32 (post-activation, pre-dropout), sets state->metrics =
+ * {loss_sum, correct, count} and adds them to state->metrics_acc.  `train` != 0 enables dropout.
+ * backward (train only) writes dW1,db1,dW2,db2 (bf16) and the CLS rows of dx (bf16 [B*S,d],
+ * other rows are zeroed here). */
+typedef struct hstd_head_args {
+  const void* x; const void* w1; const void* b1; const void* w2; const void* b2;
+  const int32_t* labels;
+  float* logits; float* dlogits; float* h; float* dz; /* fp32 [B,C], [B,C], [B,d], [B,d] */
+  void* dw1; void* db1; void* dw2; void* db2; void* dx;
+  hstd_step_state* state;
+  int32_t B, S, d, C, kind, train;
+  float p_drop;
+  uint32_t site0, site1;
+} hstd_head_args;
+int hstd_head_fwd(const hstd_head_args* args, void* stream);
+int hstd_head_bwd(const hstd_head_args* args, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
