@@ -157,6 +157,11 @@ KNOWN_MODELS = {
                                        intermediate_size=256),
     "tiny-bert": lambda: _bert(128, 2, 2, 256, vocab_size=1024),
     "tiny-roberta": lambda: _roberta(128, 2, 2, 256).replace(vocab_size=1024),
+    # smallest shapes the sm_100a kernels accept (hidden % 256 == 0, head_dim == 64)
+    "tiny-distilbert-gpu": lambda: _distil(vocab_size=2048, hidden_size=256, num_layers=2, num_heads=4,
+                                           intermediate_size=512),
+    "tiny-bert-gpu": lambda: _bert(256, 2, 4, 512, vocab_size=2048),
+    "tiny-roberta-gpu": lambda: _roberta(256, 2, 4, 512).replace(vocab_size=2048),
 }
 
 

@@ -1,0 +1,189 @@
+"""Data-parallel gradient engine: bucket plan, arenas, optimizer placement
+(reference scripts/train.py:114,133).
+
+Horovod's C++ core negotiates ready tensors, packs them into a fusion buffer and calls
+``ncclAllReduce`` + postscale; Keras then applies Adam per variable.  Here the gradient arena
+*is* the fusion buffer (parameters are laid out in backward-ready order, so a bucket is a
+contiguous byte range that completes front-to-back), and reduce + 1/world scale +
+bf16→fp32 cast + Keras-AdamW + bf16 weight write-back are one kernel per bucket:
+
+  * world_size == 1 : the flat AdamW kernel over the whole arena (no communication);
+  * mode "p2p"      : hand-written NVLink kernels over IPC-mapped peer arenas
+                      (csrc/allreduce_sm100.cu) — one-shot / two-shot / NVLS by bucket
+                      size, launched on a side stream as each bucket's gradients complete;
+  * mode "nccl"     : library all-reduce + the flat AdamW kernel — the baseline plumbing,
+                      kept for A/B measurements.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Dict, List, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+from ..ops import kernels as K
+from . import comm
+
+
+@dataclass
+class Bucket:
+    index: int
+    start: int  # element offsets into the arenas
+    end: int
+    names: List[str]
+
+    @property
+    def numel(self) -> int:
+        return self.end - self.start
+
+
+def plan_buckets(slots: Dict[str, "object"], order: List[str], bucket_elems: int, world: int) -> List[Bucket]:
+    """Greedy contiguous bucketing in backward-ready order.  Bucket boundaries fall on
+    parameter boundaries; sizes are padded by the arena alignment so every bucket splits
+    into ``world`` 16-byte-aligned slices."""
+    buckets: List[Bucket] = []
+    cur_names: List[str] = []
+    cur_start = 0
+    for n in order:
+        s = slots[n]
+        if cur_names and (s.end - cur_start) > bucket_elems:
+            buckets.append(Bucket(len(buckets), cur_start, s.offset, cur_names))
+            cur_names, cur_start = [], s.offset
+        cur_names.append(n)
+    if cur_names:
+        buckets.append(Bucket(len(buckets), cur_start, slots[order[-1]].end, cur_names))
+    return buckets
+
+
+class DPEngine:
+    def __init__(self, engine, bucket_mb: float = 32.0, mode: str = "p2p"):
+        self.engine = engine
+        self.device = engine.device
+        self.world, self.rank = comm.size(), comm.rank()
+        self.mode = mode if self.world > 1 else "local"
+        self.total = engine.total
+        order = list(engine.slots.keys())
+        self.buckets = plan_buckets(engine.slots, order, int(bucket_mb * (1 << 20) / 2), self.world)
+        self.name_to_bucket = {n: b.index for b in self.buckets for n in b.names}
+        self.distributed = False
+        self._alloc()
+
+    # ------------------------------------------------------------------ memory
+    def _alloc(self) -> None:
+        dev = self.device
+        self.p2p = None
+        if self.mode == "p2p":
+            from .p2p import P2PGroup
+
+            self.p2p = P2PGroup(self.total, self.buckets, dev)
+            self.w16, self.g16 = self.p2p.w16, self.p2p.g16
+        else:
+            self.w16 = torch.zeros(self.total, dtype=torch.bfloat16, device=dev)
+            self.g16 = torch.zeros(self.total, dtype=torch.bfloat16, device=dev)
+        # fp32 master + Adam moments.  In p2p mode each rank keeps only the slice of every
+        # bucket it owns (ZeRO-1-like); stored compactly in bucket order.
+        if self.mode == "p2p":
+            n = self.p2p.owned_elems
+        else:
+            n = self.total
+        self.master = torch.zeros(n, dtype=torch.float32, device=dev)
+        self.m = torch.zeros(n, dtype=torch.float32, device=dev)
+        self.v = torch.zeros(n, dtype=torch.float32, device=dev)
+
+    def configure(self, distributed: bool) -> None:
+        self.distributed = distributed and self.world > 1
+
+    def capturable(self) -> bool:
+        return not (self.distributed and self.mode == "nccl")
+
+    # ------------------------------------------------------------------ state movement
+    def set_master(self, flat_fp32: torch.Tensor) -> None:
+        """Install full fp32 weights (every rank passes the same tensor)."""
+        self.w16.copy_(flat_fp32.to(torch.bfloat16))
+        if self.mode == "p2p":
+            self.master.copy_(self.p2p.take_owned(flat_fp32))
+        else:
+            self.master.copy_(flat_fp32)
+        torch.cuda.synchronize()
+        comm.barrier()
+
+    def gather_master(self) -> torch.Tensor:
+        if self.mode == "p2p":
+            return self.p2p.gather_owned(self.master)
+        return self.master.clone()
+
+    def gather_moments(self) -> Tuple[torch.Tensor, torch.Tensor]:
+        if self.mode == "p2p":
+            return self.p2p.gather_owned(self.m), self.p2p.gather_owned(self.v)
+        return self.m.clone(), self.v.clone()
+
+    def set_moments(self, m: torch.Tensor, v: torch.Tensor) -> None:
+        if self.mode == "p2p":
+            self.m.copy_(self.p2p.take_owned(m))
+            self.v.copy_(self.p2p.take_owned(v))
+        else:
+            self.m.copy_(m)
+            self.v.copy_(v)
+
+    def broadcast_state(self, root: int, step_state: torch.Tensor) -> None:
+        """Rank-``root`` state to everyone (BroadcastGlobalVariablesCallback,
+        scripts/train.py:127-134).  One-time, so NCCL is fine here (K12)."""
+        if self.world <= 1:
+            return
+        full = self.gather_master()
+        dist.broadcast(full, src=root)
+        mm, vv = self.gather_moments()
+        dist.broadcast(mm, src=root)
+        dist.broadcast(vv, src=root)
+        self.set_master(full)
+        self.set_moments(mm, vv)
+        dist.broadcast(step_state, src=root)
+
+    # ------------------------------------------------------------------ hooks used while recording a plan
+    def begin_backward(self, plan) -> None:
+        self._pending = set()
+        self._done_buckets = set()
+        self._bucket_left = {b.index: set(b.names) for b in self.buckets}
+        if self.p2p is not None and self.distributed:
+            self.p2p.record_begin(plan)
+
+    def after_grads(self, plan, names: List[str]) -> None:
+        """Called (at record time) once the gradients of ``names`` have been produced."""
+        ready = []
+        for n in names:
+            b = self.name_to_bucket[n]
+            self._bucket_left[b].discard(n)
+        # head gradients are produced first and never announced separately
+        for b in self.buckets:
+            left = self._bucket_left[b.index] - {"head.out.weight", "head.out.bias", "head.dense.weight",
+                                                 "head.dense.bias"}
+            if not left and b.index not in self._done_buckets:
+                # buckets complete strictly in order because the arena is in readiness order
+                if all(i in self._done_buckets for i in range(b.index)):
+                    ready.append(b)
+                    self._done_buckets.add(b.index)
+        if self.p2p is not None and self.distributed:
+            for b in ready:
+                self.p2p.record_bucket(plan, b, self.engine.state, self.master, self.m, self.v)
+
+    def end_backward(self, plan) -> None:
+        assert len(self._done_buckets) == len(self.buckets), "every bucket must be complete at end of backward"
+        st = self.engine.state
+        if self.p2p is not None and self.distributed:
+            self.p2p.record_end(plan)
+            return
+        if self.mode == "p2p":
+            # p2p arenas but a non-distributed optimizer (e.g. world>1 without DistributedOptimizer)
+            # still owns only its slice of master state: run the local update on owned slices
+            self.p2p.record_local_update(plan, st, self.master, self.m, self.v)
+            return
+        if self.distributed:  # nccl baseline plumbing
+            g = self.g16
+            plan.launches += 1
+            plan.ops.append(lambda: dist.all_reduce(g))
+            scale = 1.0 / self.world
+        else:
+            scale = 1.0
+        plan.launches += 1
+        plan.ops.append(lambda: K.adamw_flat(st, self.g16, self.master, self.m, self.v, self.w16, scale))

@@ -66,17 +66,27 @@ class History:
 
 
 class _Meter:
-    """Running (loss_sum, correct, count) on the device; one host read per ``read()``."""
+    """Running (loss_sum, correct, count) on the device; one host read per ``read()``.
+    The engine backend accumulates inside its own kernels (``train_step`` returns None)."""
 
-    def __init__(self, device: torch.device):
-        self.acc = torch.zeros(3, dtype=torch.float64, device=device)
+    def __init__(self, device: torch.device, backend=None):
+        self.backend = backend if hasattr(backend, "read_metrics") else None
+        if self.backend is not None:
+            self.backend.reset_metrics()
+        else:
+            self.acc = torch.zeros(3, dtype=torch.float64, device=device)
 
-    def update(self, loss_sum, correct, count) -> None:
+    def update(self, res) -> None:
+        if res is None:
+            return
+        loss_sum, correct, count = res
         self.acc[0] += loss_sum.to(self.acc.dtype) if torch.is_tensor(loss_sum) else loss_sum
         self.acc[1] += correct.to(self.acc.dtype) if torch.is_tensor(correct) else correct
         self.acc[2] += count.to(self.acc.dtype) if torch.is_tensor(count) else count
 
     def read(self) -> Dict[str, float]:
+        if self.backend is not None:
+            return self.backend.read_metrics()
         l, c, n = self.acc.tolist()
         n = max(n, 1.0)
         return {"loss": l / n, "sparse_categorical_accuracy": c / n, "count": n}
@@ -125,12 +135,12 @@ class SequenceClassifier:
         t_fit = time.time()
         samples_seen = 0
         for epoch in range(epochs):
-            meter = _Meter(device)
+            meter = _Meter(device, self.backend)
             t0 = time.time()
             for step, (feats, labels) in enumerate(dataset):
                 if step >= steps:
                     break
-                meter.update(*self.backend.train_step(feats, labels))
+                meter.update(self.backend.train_step(feats, labels))
                 if verbose and log_every > 0 and (step + 1) % log_every == 0:
                     r = meter.read()
                     dt = time.time() - t0
@@ -158,12 +168,12 @@ class SequenceClassifier:
 
     def evaluate(self, dataset: BatchedDataset, batch_size: Optional[int] = None, return_dict: bool = False,
                  verbose: int = 0, steps: Optional[int] = None, **_ignored):
-        meter = _Meter(self.backend.device)
+        meter = _Meter(self.backend.device, self.backend)
         n = len(dataset) if steps is None else min(steps, len(dataset))
         for step, (feats, labels) in enumerate(dataset):
             if step >= n:
                 break
-            meter.update(*self.backend.eval_step(feats, labels))
+            meter.update(self.backend.eval_step(feats, labels))
         r = meter.read()
         r.pop("count")
         self._sink({"event": "evaluate", **r})
