@@ -66,9 +66,10 @@ def position_ids_for(cfg: EncoderConfig, input_ids: torch.Tensor) -> torch.Tenso
 
 
 class EncoderForSequenceClassification(nn.Module):
-    def __init__(self, cfg: EncoderConfig):
+    def __init__(self, cfg: EncoderConfig, sdpa: bool = False):
         super().__init__()
         self.cfg = cfg
+        self.sdpa = sdpa  # library fused attention (used by the DDP baseline only)
         self.emb = _Embeddings(cfg)
         self.layers = nn.ModuleList(_Layer(cfg) for _ in range(cfg.num_layers))
         self.head = _Head(cfg)
@@ -106,9 +107,14 @@ class EncoderForSequenceClassification(nn.Module):
         for lyr in self.layers:
             qkv = lyr.qkv(x).view(B, S, 3, H, dh)
             q, k, v = (qkv[:, :, i].transpose(1, 2) for i in range(3))  # [B,H,S,dh]
-            scores = torch.matmul(q, k.transpose(-1, -2)) / math.sqrt(dh) + bias
-            probs = F.dropout(torch.softmax(scores, dim=-1), cfg.attention_dropout, self.training)
-            ctx = torch.matmul(probs, v).transpose(1, 2).reshape(B, S, H * dh)
+            if self.sdpa:
+                ctx = F.scaled_dot_product_attention(
+                    q, k, v, attn_mask=bias, dropout_p=cfg.attention_dropout if self.training else 0.0)
+                ctx = ctx.transpose(1, 2).reshape(B, S, H * dh)
+            else:
+                scores = torch.matmul(q, k.transpose(-1, -2)) / math.sqrt(dh) + bias
+                probs = F.dropout(torch.softmax(scores, dim=-1), cfg.attention_dropout, self.training)
+                ctx = torch.matmul(probs, v).transpose(1, 2).reshape(B, S, H * dh)
             a = F.dropout(lyr.out(ctx), post_attn_dropout, self.training)
             x = lyr.ln1(a + x)
             f = lyr.ffn2(F.gelu(lyr.ffn1(x)))
