@@ -8,6 +8,9 @@
 // dropout / gather inside model.fit (scripts/train.py:145).
 #include <cub/block/block_scan.cuh>
 
+#include <mutex>
+#include <string>
+
 #include "common.cuh"
 #include "device_utils.cuh"
 
@@ -472,4 +475,63 @@ extern "C" HSTD_API int hstd_embed_bwd(const void* de, const int32_t* ids, const
                                 static_cast<const __nv_bfloat16*>(de), ids, pos_ids,
                                 static_cast<__nv_bfloat16*>(word_grad), static_cast<__nv_bfloat16*>(pos_grad), M, d));
   return check_launch("embed_bwd");
+}
+
+// ------------------------------------------------------------------ column sums without a workspace
+// Some users of this library cannot hand us scratch memory and must not cause a device
+// allocation: a C caller that has no device allocator of its own to draw a workspace from, or
+// a process whose HBM is entirely owned by another pool (the training framework's caching
+// allocator, an inference server) so that a stray cudaMalloc would fail or, worse, force an
+// implicit device-wide synchronisation in the middle of an overlapped step.  For them the
+// per-row-group partial sums live in this fixed array instead of a caller buffer.  It is part
+// of the library image: every GPU that loads libhstd_b200.so carries these 512 KiB until the
+// process exits.
+constexpr int COLSUM_NOALLOC_MAX_N = 4096;  // widest matrix the fixed scratch can serve
+static __device__ __align__(256) float g_colsum_noalloc_scratch[COLSUM_ROWGROUPS * COLSUM_NOALLOC_MAX_N];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_noalloc_mu;
+float* g_noalloc_scratch_ptr[kMaxDevices] = {};
+
+// The array's name is only a host-side handle; the device address has to be asked for, once
+// per device and with that device current (each GPU has its own copy of the array).
+int colsum_noalloc_scratch(float** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return set_error(-6, std::string("colsum_noalloc: cudaGetDevice: ") + cudaGetErrorString(e));
+  if (dev < 0 || dev >= kMaxDevices) return set_error(-1, "colsum_noalloc: device ordinal out of range");
+  std::lock_guard<std::mutex> g(g_noalloc_mu);
+  if (g_noalloc_scratch_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_colsum_noalloc_scratch);
+    if (e != cudaSuccess || p == nullptr)
+      return set_error(-6, std::string("colsum_noalloc: cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+    g_noalloc_scratch_ptr[dev] = static_cast<float*>(p);
+  }
+  *out = g_noalloc_scratch_ptr[dev];
+  return 0;
+}
+}  // namespace
+
+extern "C" HSTD_API int hstd_colsum_noalloc_max_n(void) { return COLSUM_NOALLOC_MAX_N; }
+
+extern "C" HSTD_API int hstd_colsum_noalloc(const void* x, int64_t ld, int M, int N, void* out, void* stream) {
+  if (N % 8 != 0) return set_error(-1, "colsum_noalloc: N must be a multiple of 8");
+  if (N > COLSUM_NOALLOC_MAX_N)
+    return set_error(-1, "colsum_noalloc: N = " + std::to_string(N) + " exceeds the built-in scratch (max N = " +
+                             std::to_string(COLSUM_NOALLOC_MAX_N) + "); use hstd_colsum with a caller workspace");
+  if (M <= 0 || N <= 0) return set_error(-1, "colsum_noalloc: empty matrix");
+  float* scratch = nullptr;
+  if (int rc = colsum_noalloc_scratch(&scratch)) return rc;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  // Nothing in the scratch has to start at zero: the first kernel overwrites every
+  // (row group, column < N) cell the second one reads, so leftovers of an earlier, wider
+  // call are never observed.
+  dim3 grid((N + 255) / 256, COLSUM_ROWGROUPS);
+  colsum_partial_kernel<<<grid, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(x), ld, M, N, scratch);
+  if (int rc = check_launch("colsum_noalloc")) return rc;
+  partials_finalize_kernel<<<(N + 255) / 256, 256, 0, s>>>(scratch, COLSUM_ROWGROUPS, N, N,
+                                                           static_cast<__nv_bfloat16*>(out), nullptr, nullptr);
+  return check_launch("colsum_noalloc finalize");
 }

@@ -153,6 +153,24 @@ int64_t hstd_ln_bwd_partials_floats(int d);
 int hstd_colsum(const void* x, int64_t ld, int M, int N, void* out_bf16, float* partials, void* stream);
 int64_t hstd_colsum_partials_floats(int N);
 
+/* Column sums for callers that can neither pass a workspace nor tolerate a device allocation
+ * (no counterpart in the reference, which has no native code at all): a plain-C user with no
+ * device allocator to carve scratch from, or a process whose GPU memory is wholly owned by
+ * another pool, where a cudaMalloc from inside a library could fail or stall every stream with
+ * its implicit synchronisation.  Same result as hstd_colsum, but the partial sums are kept in a
+ * 512 KiB array that is built into the library and resident on every GPU that loads it, so:
+ *   - N is limited to hstd_colsum_noalloc_max_n() (4096); larger N is refused with an error
+ *     and should go through hstd_colsum;
+ *   - the call makes no cudaMalloc/cudaFree and uses no allocating library routine;
+ *   - the first call on each device looks up the array's device address (with that device
+ *     current); make that first call before starting any stream capture;
+ *   - all calls on a device share the one array: two calls whose kernels can run at the same
+ *     time (different streams, no dependency between them) race on it — order them.  The
+ *     array keeps the previous call's partial sums; nothing needs clearing, every cell that is
+ *     read is first rewritten by the same call. */
+int hstd_colsum_noalloc(const void* x, int64_t ld, int M, int N, void* out_bf16, void* stream);
+int hstd_colsum_noalloc_max_n(void);
+
 /* ------------------------------------------------------------------ attention softmax (K3)
  * scores: bf16 [B,H,Sq,Sk] (already scaled), key mask int32 [B,Sk] (1 = attend).
  * forward : P = softmax(scores + mask) written in place; Pd = dropout(P) written to `pd`
