@@ -495,3 +495,4 @@ class EngineBackend:
 
     def finish(self) -> None:
         torch.cuda.synchronize()
+        self.dp.check_errors()

@@ -97,6 +97,16 @@ class DPEngine:
     def capturable(self) -> bool:
         return not (self.distributed and self.mode == "nccl")
 
+    def check_errors(self) -> None:
+        if self.p2p is not None:
+            self.p2p.check_errors()
+
+    def describe(self) -> dict:
+        d = {"mode": self.mode, "world": self.world, "num_buckets": len(self.buckets)}
+        if self.p2p is not None:
+            d.update(self.p2p.describe())
+        return d
+
     # ------------------------------------------------------------------ state movement
     def set_master(self, flat_fp32: torch.Tensor) -> None:
         """Install full fp32 weights (every rank passes the same tensor)."""
@@ -165,7 +175,8 @@ class DPEngine:
                     self._done_buckets.add(b.index)
         if self.p2p is not None and self.distributed:
             for b in ready:
-                self.p2p.record_bucket(plan, b, self.engine.state, self.master, self.m, self.v)
+                self.p2p.record_bucket(plan, b, self.engine.state, self.master, self.m, self.v,
+                                       overlap=self.engine.overlap)
 
     def end_backward(self, plan) -> None:
         assert len(self._done_buckets) == len(self.buckets), "every bucket must be complete at end of backward"
@@ -174,10 +185,9 @@ class DPEngine:
             self.p2p.record_end(plan)
             return
         if self.mode == "p2p":
-            # p2p arenas but a non-distributed optimizer (e.g. world>1 without DistributedOptimizer)
-            # still owns only its slice of master state: run the local update on owned slices
-            self.p2p.record_local_update(plan, st, self.master, self.m, self.v)
-            return
+            raise NotImplementedError(
+                "world_size > 1 with the p2p arenas shards the optimizer state across ranks, so the optimizer must "
+                "be wrapped in hvd.DistributedOptimizer (or pass comm='nccl' for independent replicas)")
         if self.distributed:  # nccl baseline plumbing
             g = self.g16
             plan.launches += 1

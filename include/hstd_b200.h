@@ -211,6 +211,47 @@ typedef struct hstd_head_args {
 int hstd_head_fwd(const hstd_head_args* args, void* stream);
 int hstd_head_bwd(const hstd_head_args* args, void* stream);
 
+/* ------------------------------------------------------------------ fused gradient all-reduce (K9, K10, K11)
+ * One launch per gradient bucket [start, start+numel) of the flat arenas.  Replaces
+ * hvd.DistributedOptimizer's ncclAllReduce + 1/size postscale and Keras' per-variable Adam
+ * apply (reference scripts/train.py:113-114) with one NVLink peer-memory kernel:
+ * reduce (peer loads or in-switch multimem.ld_reduce) -> x 1/world -> bf16->fp32 -> Keras-AdamW on
+ * the owned fp32 master/m/v -> bf16 weights stored to every rank (peer stores / multimem.st).
+ * g_peers / w_peers / flag_peers: the same arena as mapped from every rank (index = rank;
+ * entry [rank] is the local pointer).  flag area: hstd_allreduce_flag_words(num_buckets)
+ * zero-initialised uint32 per rank; epoch: hstd_allreduce_max_blocks() zeroed uint32 per bucket
+ * (local); error: one zeroed uint32 (local) that becomes non-zero if a peer never arrived.
+ * master/m/v point at this bucket's *owned* range: numel/world elements (rank-th slice) for
+ * TWO_SHOT and NVLS, numel elements (replicated) for ONE_SHOT and LOCAL.
+ * update == 0 turns the kernel into a plain averaging all-reduce of the gradient arena
+ * (ONE_SHOT writes its result to the weight arena instead: it cannot be in place). */
+enum { HSTD_AR_LOCAL = 0, HSTD_AR_TWO_SHOT = 1, HSTD_AR_ONE_SHOT = 2, HSTD_AR_NVLS = 3 };
+typedef struct hstd_allreduce_args {
+  void* g_peers[8];
+  void* w_peers[8];
+  void* flag_peers[8];
+  void* g_mc; /* multicast mapping of the gradient / weight arenas (NVLS only) */
+  void* w_mc;
+  void* epoch;
+  void* error;
+  float* master; float* m; float* v;
+  const hstd_step_state* state;
+  int64_t start, numel; /* elements; numel % (8*world) == 0 */
+  int32_t world, rank, bucket_index, mode, update, blocks;
+} hstd_allreduce_args;
+int hstd_fused_allreduce(const hstd_allreduce_args* args, void* stream);
+int hstd_allreduce_max_blocks(void);
+int64_t hstd_allreduce_flag_words(int num_buckets);
+
+/* CUDA IPC plumbing for the symmetric arenas (the C++ side of what MPI + NCCL bootstrap do for
+ * the reference, launch.py:22 / scripts/train.py:24): allocate a zeroed device arena and export
+ * its 64-byte handle; open a peer's handle; close / free. */
+int hstd_ipc_alloc(int64_t bytes, void** ptr, void* handle64);
+int hstd_ipc_open(const void* handle64, void** ptr);
+int hstd_ipc_close(void* ptr);
+int hstd_ipc_free(void* ptr);
+int hstd_enable_peer_access(int dev, int peer);
+
 #ifdef __cplusplus
 }
 #endif

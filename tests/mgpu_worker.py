@@ -1,0 +1,145 @@
+"""Multi-GPU worker run under torchrun by tests/test_multigpu.py (one process per GPU).
+Each check prints 'OK <name>' or raises; rank 0's stdout is what the test asserts on."""
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+import huggingface_sagemaker_tensorflow_distributed_b200.parallel.hvd as hvd  # noqa: E402
+from huggingface_sagemaker_tensorflow_distributed_b200.ops import kernels as K  # noqa: E402
+from huggingface_sagemaker_tensorflow_distributed_b200.parallel import comm, p2p  # noqa: E402
+from huggingface_sagemaker_tensorflow_distributed_b200.parallel.dp_engine import Bucket  # noqa: E402
+
+
+def log(*a):
+    if hvd.rank() == 0:
+        print(*a, flush=True)
+
+
+def gather_all(t):
+    parts = [torch.empty_like(t) for _ in range(hvd.size())]
+    dist.all_gather(parts, t.contiguous())
+    return parts
+
+
+def check_collectives():
+    W, R, dev = hvd.size(), hvd.rank(), comm.device()
+    sizes = [64 * W, 1024 * 8, 1 << 20, (3 << 20) + 128 * W]
+    sizes = [s // (8 * W) * (8 * W) for s in sizes]
+    starts, off = [], 0
+    for s in sizes:
+        starts.append(off)
+        off += s
+    buckets = [Bucket(i, st, st + n, []) for i, (st, n) in enumerate(zip(starts, sizes))]
+    grp = p2p.P2PGroup(off, buckets, dev)
+    log("arena", grp.arena.kind, "nvls", bool(grp.arena.mc_ptr))
+    modes = [p2p.AR_TWO_SHOT, p2p.AR_ONE_SHOT] + ([p2p.AR_NVLS] if grp.arena.mc_ptr else [])
+    for mode in modes:
+        for rep in range(3):  # repeated calls exercise the epoch protocol
+            torch.manual_seed(100 * rep + R)
+            grp.g16.copy_((torch.randn(off, device=dev) * (1 + R)).bfloat16())
+            grp.w16.zero_()
+            torch.cuda.synchronize()
+            dist.barrier()
+            want = torch.stack([p.float() for p in gather_all(grp.g16)]).sum(0) / W
+            dist.barrier()
+            for b in buckets:
+                grp.launch(grp.make_args(b.index, b.start, b.numel, mode, update=False))
+            torch.cuda.synchronize()
+            dist.barrier()
+            got = grp.w16 if mode == p2p.AR_ONE_SHOT else grp.g16
+            err = (got.float() - want).abs().max().item()
+            assert err <= 0.02 * want.abs().max().item(), (p2p.MODE_NAMES[mode], rep, err)
+            same = gather_all(got)
+            assert all(torch.equal(same[0], s) for s in same), f"ranks disagree in {p2p.MODE_NAMES[mode]}"
+            grp.check_errors()
+        log("OK allreduce", p2p.MODE_NAMES[mode])
+    # fused update vs. (reference all-reduce + flat AdamW)
+    for mode in modes:
+        grp2 = p2p.P2PGroup(off, buckets, dev, force_mode=mode)
+        torch.manual_seed(7)
+        w0 = torch.randn(off, device=dev)
+        master = grp2.take_owned(w0)
+        m, v = torch.zeros_like(master), torch.zeros_like(master)
+        grp2.w16.copy_(w0.bfloat16())
+        rm, rmm, rv = w0.clone(), torch.zeros(off, device=dev), torch.zeros(off, device=dev)
+        rw = torch.empty(off, dtype=torch.bfloat16, device=dev)
+        st = K.new_step_state(dev, seed=1)
+        for step in range(3):
+            torch.manual_seed(1000 + 10 * step + R)
+            grp2.g16.copy_((torch.randn(off, device=dev) * 0.1).bfloat16())
+            torch.cuda.synchronize()
+            dist.barrier()
+            avg = (torch.stack([p.float() for p in gather_all(grp2.g16)]).sum(0) / W)
+            K.step_prologue(st, 1e-2, "constant", 0, 0, 0.9, 0.999, 1e-7, 0.01)
+            for b in buckets:
+                _, _, o = grp2.owned[b.index]
+                grp2.launch(grp2.make_args(b.index, b.start, b.numel, grp2.modes[b.index], True, st, master, m, v, o))
+            torch.cuda.synchronize()
+            dist.barrier()
+            # the kernel rounds the average to fp32 (two-shot/one-shot) or bf16 (NVLS switch output)
+            gref = avg.bfloat16() if mode == p2p.AR_NVLS else avg
+            K.adamw_flat(st, gref.bfloat16() if mode == p2p.AR_NVLS else avg.bfloat16(), rm, rmm, rv, rw) \
+                if mode == p2p.AR_NVLS else _ref_adam(st, avg, rm, rmm, rv, rw)
+            torch.cuda.synchronize()
+        full = grp2.gather_owned(master)
+        tol = 2e-3 if mode == p2p.AR_NVLS else 1e-5
+        assert torch.allclose(full, rm, atol=tol, rtol=tol), (p2p.MODE_NAMES[mode], (full - rm).abs().max().item())
+        same = gather_all(grp2.w16)
+        assert all(torch.equal(same[0], s) for s in same)
+        assert (grp2.w16.float() - rm).abs().max().item() <= 0.02 * rm.abs().max().item()
+        grp2.check_errors()
+        log("OK fused_update", p2p.MODE_NAMES[mode])
+
+
+def _ref_adam(st, g_fp32, w, m, v, wb):
+    s = K.read_step_state(st)
+    m.mul_(s.beta1).add_(g_fp32, alpha=1 - s.beta1)
+    v.mul_(s.beta2).addcmul_(g_fp32, g_fp32, value=1 - s.beta2)
+    w.mul_(s.decay).addcdiv_(m, v.sqrt() + s.eps, value=-s.lr_t)
+    wb.copy_(w.bfloat16())
+
+
+def check_training():
+    from huggingface_sagemaker_tensorflow_distributed_b200 import trainer as T
+    from huggingface_sagemaker_tensorflow_distributed_b200.data import BatchedDataset, synthetic_imdb
+    from huggingface_sagemaker_tensorflow_distributed_b200.optim import Adam
+    W, R, dev = hvd.size(), hvd.rank(), comm.device()
+    losses = {}
+    for comm_mode in ("p2p", "nccl"):
+        model = T.AutoModelForSequenceClassification.from_pretrained(
+            "tiny-distilbert-gpu", device=dev, dropout=0.0, seed=5 + R, comm_mode=comm_mode, bucket_mb=0.5)
+        ds = synthetic_imdb(model.cfg, 16 * 4 * W, 128, seed=2)
+        opt = hvd.DistributedOptimizer(Adam(learning_rate=1e-4 * W))
+        model.compile(optimizer=opt, loss=T.SparseCategoricalCrossentropy(from_logits=True))
+        hist = model.fit(BatchedDataset(ds, 4, R, W), epochs=2, verbose=0,
+                         callbacks=[hvd.callbacks.BroadcastGlobalVariablesCallback(0)])
+        losses[comm_mode] = hist.history["loss"]
+        sd = model.state_dict()
+        flat = torch.cat([v.reshape(-1) for v in sd.values()]).to(dev)
+        same = gather_all(flat)
+        assert all(torch.equal(same[0], s) for s in same), f"weights diverged across ranks ({comm_mode})"
+        if comm_mode == "p2p":
+            log("dp:", model.backend.dp.describe())
+            assert model.backend.plans[(4, 128, True)].graph is not None
+            p2p_flat = flat.clone()
+        else:
+            assert (flat - p2p_flat).abs().max().item() < 5e-3, (flat - p2p_flat).abs().max().item()
+    lp, ln = losses["p2p"], losses["nccl"]
+    assert abs(lp[-1] - ln[-1]) < 2e-2, losses
+    log("OK training p2p==nccl", lp, ln)
+
+
+if __name__ == "__main__":
+    hvd.init()
+    which = sys.argv[1] if len(sys.argv) > 1 else "all"
+    if which in ("all", "collectives"):
+        check_collectives()
+    if which in ("all", "training"):
+        check_training()
+    dist.barrier()
+    log("ALL OK")
+    hvd.shutdown()
