@@ -67,6 +67,7 @@ class DPEngine:
         self.buckets = plan_buckets(engine.slots, order, int(bucket_mb * (1 << 20) / 2), self.world)
         self.name_to_bucket = {n: b.index for b in self.buckets for n in b.names}
         self.distributed = False
+        self._pending_full = None
         self._alloc()
 
     # ------------------------------------------------------------------ memory
@@ -109,7 +110,11 @@ class DPEngine:
 
     # ------------------------------------------------------------------ state movement
     def set_master(self, flat_fp32: torch.Tensor) -> None:
-        """Install full fp32 weights (every rank passes the same tensor)."""
+        """Install full fp32 weights.  With sharded optimizer state a rank keeps fp32 only for
+        the slices it owns, so until training starts a host copy of what *this* rank was given
+        is retained: a later broadcast_state(root) can then ship root's complete fp32 tensor
+        even if ranks were initialised differently."""
+        self._pending_full = flat_fp32.detach().cpu() if self.mode == "p2p" else None
         self.w16.copy_(flat_fp32.to(torch.bfloat16))
         if self.mode == "p2p":
             self.master.copy_(self.p2p.take_owned(flat_fp32))
@@ -141,7 +146,8 @@ class DPEngine:
         scripts/train.py:127-134).  One-time, so NCCL is fine here (K12)."""
         if self.world <= 1:
             return
-        full = self.gather_master()
+        pending = getattr(self, "_pending_full", None)
+        full = pending.to(self.device) if pending is not None else self.gather_master()
         dist.broadcast(full, src=root)
         mm, vv = self.gather_moments()
         dist.broadcast(mm, src=root)
@@ -179,6 +185,7 @@ class DPEngine:
                                        overlap=self.engine.overlap)
 
     def end_backward(self, plan) -> None:
+        self._pending_full = None  # training is about to start: sharded state is now the truth
         assert len(self._done_buckets) == len(self.buckets), "every bucket must be complete at end of backward"
         st = self.engine.state
         if self.p2p is not None and self.distributed:
