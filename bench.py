@@ -118,8 +118,10 @@ def main() -> None:
         comm.allreduce_max_(ms)
         return ms[0].item(), ms[1].item()
 
-    sampler = ClockSampler(gpu_index=torch.cuda.current_device(),
+    sampler = ClockSampler(gpu_index=torch.cuda.current_device(), period_ms=100,
                            out_csv="gpurun_out/clocks.csv" if rank == 0 and os.path.isdir("gpurun_out") else None)
+    sampler.start()  # nvidia-smi needs a second to come up: start before warm-up, keep it through the timed regions
+    t_sampler = time.perf_counter()
     extra = {}
     if a.impl == "ddp":
         sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "baseline"))
@@ -129,7 +131,6 @@ def main() -> None:
         dbatches = [(f["input_ids"].to(dev).long(), f["attention_mask"].to(dev), l.to(dev).long()) for f, l in batches]
         for i in range(W):
             ddp_baseline.train_step(model, opt, *dbatches[i % nb])
-        sampler.start()
         dev_ms, _ = timed(lambda i: ddp_baseline.train_step(model, opt, *dbatches[i % nb]), K)
 
         def e2e_step(i):
@@ -140,6 +141,9 @@ def main() -> None:
             loss.item()
 
         e2e_ms, _ = timed(e2e_step, K)
+        while time.perf_counter() - t_sampler < 4.0:  # untimed: keep the load on until the sampler has data
+            ddp_baseline.train_step(model, opt, *dbatches[0])
+            torch.cuda.synchronize()
         clocks = sampler.stop()
         launches = None
         parallelism = f"ddp{world}-nccl"
@@ -156,7 +160,6 @@ def main() -> None:
         for i in range(W):
             eng.train_step(*batches[i % nb])
         plan = eng.plans[(B, S, True)]
-        sampler.start()
         # device-resident inputs (the last staged batch): kernels only
         dev_ms, _ = timed(lambda i: eng._run(plan), K)
 
@@ -166,6 +169,9 @@ def main() -> None:
             eng.last_step_metrics().cpu()
 
         e2e_ms, _ = timed(e2e_step, K)
+        while time.perf_counter() - t_sampler < 4.0:  # untimed: keep the load on until the sampler has data
+            eng._run(plan)
+            torch.cuda.synchronize()
         clocks = sampler.stop()
         launches = plan.launches * K
         parallelism = f"dp{world}" + ("" if world == 1 else f"-{eng.dp.mode}")
