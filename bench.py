@@ -121,7 +121,6 @@ def main() -> None:
     sampler = ClockSampler(gpu_index=torch.cuda.current_device(), period_ms=100,
                            out_csv="gpurun_out/clocks.csv" if rank == 0 and os.path.isdir("gpurun_out") else None)
     sampler.start()  # nvidia-smi needs a second to come up: start before warm-up, keep it through the timed regions
-    t_sampler = time.perf_counter()
     extra = {}
     if a.impl == "ddp":
         sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "baseline"))
@@ -141,9 +140,11 @@ def main() -> None:
             loss.item()
 
         e2e_ms, _ = timed(e2e_step, K)
-        while time.perf_counter() - t_sampler < 4.0:  # untimed: keep the load on until the sampler has data
+        # untimed: ~2.5 s more of the same load so the 100 ms clock sampler sees it.  The count is
+        # derived from the all-reduced step time, hence identical on every rank.
+        for _ in range(min(5000, int(2500.0 / max(dev_ms / K, 1e-3)) + 1)):
             ddp_baseline.train_step(model, opt, *dbatches[0])
-            torch.cuda.synchronize()
+        torch.cuda.synchronize()
         clocks = sampler.stop()
         launches = None
         parallelism = f"ddp{world}-nccl"
@@ -169,9 +170,11 @@ def main() -> None:
             eng.last_step_metrics().cpu()
 
         e2e_ms, _ = timed(e2e_step, K)
-        while time.perf_counter() - t_sampler < 4.0:  # untimed: keep the load on until the sampler has data
+        # untimed: ~2.5 s more of the same load so the 100 ms clock sampler sees it.  The count is
+        # derived from the all-reduced step time, hence identical on every rank.
+        for _ in range(min(5000, int(2500.0 / max(dev_ms / K, 1e-3)) + 1)):
             eng._run(plan)
-            torch.cuda.synchronize()
+        torch.cuda.synchronize()
         clocks = sampler.stop()
         launches = plan.launches * K
         parallelism = f"dp{world}" + ("" if world == 1 else f"-{eng.dp.mode}")

@@ -152,17 +152,28 @@ __global__ void __launch_bounds__(256) head_bwd_dw1_kernel(const hstd_head_args 
   if (k == 0) static_cast<__nv_bfloat16*>(p.db1)[j] = __float2bfloat16_rn(accb);
 }
 
-// dx[b*S, k] = drop0'( sum_j dz[b,j] * W1[j,k] ).  thread per (b,k)
-__global__ void __launch_bounds__(256) head_bwd_dx_kernel(const hstd_head_args p) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= p.B * p.d) return;
-  const int b = i / p.d, k = i - b * p.d;
-  const Dropout d0 = make_dropout(p.state, p.kind == 2 ? p.p_drop : 0.f, p.site0);
+// dx[b*S, k] = drop0'( sum_j dz[b,j] * W1[j,k] ).  grid (d/128, B); block = 128 columns x 8
+// j-groups, combined through smem (the j loop is the long dimension: d sequential loads).
+constexpr int HDX_COLS = 128, HDX_GROUPS = 8;
+__global__ void __launch_bounds__(HDX_COLS * HDX_GROUPS) head_bwd_dx_kernel(const hstd_head_args p) {
+  const int lc = threadIdx.x % HDX_COLS, grp = threadIdx.x / HDX_COLS;
+  const int k = blockIdx.x * HDX_COLS + lc, b = blockIdx.y;
   const __nv_bfloat16* w1 = static_cast<const __nv_bfloat16*>(p.w1);
   float acc = 0.f;
-  for (int j = 0; j < p.d; ++j) acc += p.dz[b * p.d + j] * __bfloat162float(w1[int64_t(j) * p.d + k]);
-  acc *= drop_mult(d0, uint64_t(b) * p.d + k);
-  static_cast<__nv_bfloat16*>(p.dx)[int64_t(b) * p.S * p.d + k] = __float2bfloat16_rn(acc);
+  if (k < p.d) {
+#pragma unroll 4
+    for (int j = grp; j < p.d; j += HDX_GROUPS) acc += p.dz[b * p.d + j] * __bfloat162float(w1[int64_t(j) * p.d + k]);
+  }
+  __shared__ float red[HDX_GROUPS][HDX_COLS];
+  red[grp][lc] = acc;
+  __syncthreads();
+  if (grp == 0 && k < p.d) {
+#pragma unroll
+    for (int g = 1; g < HDX_GROUPS; ++g) acc += red[g][lc];
+    const Dropout d0 = make_dropout(p.state, p.kind == 2 ? p.p_drop : 0.f, p.site0);
+    acc *= drop_mult(d0, uint64_t(b) * p.d + k);
+    static_cast<__nv_bfloat16*>(p.dx)[int64_t(b) * p.S * p.d + k] = __float2bfloat16_rn(acc);
+  }
 }
 
 }  // namespace hstd
@@ -190,6 +201,6 @@ extern "C" HSTD_API int hstd_head_bwd(const hstd_head_args* a, void* stream) {
   if (int rc = check_launch("head_bwd_dz")) return rc;
   head_bwd_dw1_kernel<<<dim3((a->d + 255) / 256, a->d), 256, 0, s>>>(*a);
   if (int rc = check_launch("head_bwd_dw1")) return rc;
-  head_bwd_dx_kernel<<<(a->B * a->d + 255) / 256, 256, 0, s>>>(*a);
+  head_bwd_dx_kernel<<<dim3((a->d + HDX_COLS - 1) / HDX_COLS, a->B), HDX_COLS * HDX_GROUPS, 0, s>>>(*a);
   return check_launch("head_bwd_dx");
 }

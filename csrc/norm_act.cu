@@ -190,16 +190,29 @@ __global__ void __launch_bounds__(LN_WARPS * 32) ln_bwd_kernel(const hstd_ln_bwd
 }
 
 // Sum `nparts` partial rows of `width` floats and scatter segments of `seg` columns to up
-// to three bf16 destinations (dst[k] may be null).
-__global__ void partials_finalize_kernel(const float* __restrict__ partials, int nparts, int width, int seg,
-                                         __nv_bfloat16* d0, __nv_bfloat16* d1, __nv_bfloat16* d2) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= width) return;
+// to three bf16 destinations (dst[k] may be null).  Block = 32 columns x 8 part-groups:
+// coalesced 128-byte row reads, eight independent partial sums per column, smem combine.
+constexpr int FIN_COLS = 32, FIN_GROUPS = 8;
+__global__ void __launch_bounds__(FIN_COLS * FIN_GROUPS)
+partials_finalize_kernel(const float* __restrict__ partials, int nparts, int width, int seg, __nv_bfloat16* d0,
+                         __nv_bfloat16* d1, __nv_bfloat16* d2) {
+  const int lc = threadIdx.x & (FIN_COLS - 1), grp = threadIdx.x / FIN_COLS;
+  const int c = blockIdx.x * FIN_COLS + lc;
   float s = 0.f;
-  for (int i = 0; i < nparts; ++i) s += partials[int64_t(i) * width + c];
-  const int k = c / seg;
-  __nv_bfloat16* dst = k == 0 ? d0 : (k == 1 ? d1 : d2);
-  if (dst) dst[c - k * seg] = __float2bfloat16_rn(s);
+  if (c < width) {
+#pragma unroll 4
+    for (int i = grp; i < nparts; i += FIN_GROUPS) s += partials[int64_t(i) * width + c];
+  }
+  __shared__ float red[FIN_GROUPS][FIN_COLS];
+  red[grp][lc] = s;
+  __syncthreads();
+  if (grp == 0 && c < width) {
+#pragma unroll
+    for (int g = 1; g < FIN_GROUPS; ++g) s += red[g][lc];
+    const int k = c / seg;
+    __nv_bfloat16* dst = k == 0 ? d0 : (k == 1 ? d1 : d2);
+    if (dst) dst[c - k * seg] = __float2bfloat16_rn(s);
+  }
 }
 
 // ------------------------------------------------------------------ column sums
@@ -362,11 +375,21 @@ __global__ void __launch_bounds__(256) embed_bwd_kernel(const __nv_bfloat16* __r
   const int row = blockIdx.x * 8 + warp;
   if (row >= M) return;
   const int id = ids[row], pid = pos_ids[row];
+  uint4 u[NV];
+  bool nz = false;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    u[i] = *reinterpret_cast<const uint4*>(de + int64_t(row) * d + i * 256 + lane * 8);
+    // +0.0 / -0.0 both count as zero
+    nz |= ((u[i].x | u[i].y | u[i].z | u[i].w) & 0x7FFF7FFFu) != 0;
+  }
+  // Padding positions receive an exactly-zero gradient (nothing attends to them and only the
+  // CLS row is pooled); skipping them removes the atomic pile-up on the [PAD] embedding row.
+  if (!__any_sync(0xffffffffu, nz)) return;
 #pragma unroll
   for (int i = 0; i < NV; ++i) {
     const int col = i * 256 + lane * 8;
-    const uint4 u = *reinterpret_cast<const uint4*>(de + int64_t(row) * d + col);
-    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u[i]);
     __nv_bfloat162* w = reinterpret_cast<__nv_bfloat162*>(word_grad + int64_t(id) * d + col);
     __nv_bfloat162* q = reinterpret_cast<__nv_bfloat162*>(pos_grad + int64_t(pid) * d + col);
 #pragma unroll
@@ -417,7 +440,7 @@ extern "C" HSTD_API int hstd_ln_bwd(const hstd_ln_bwd_args* a, void* stream) {
   HSTD_DISPATCH_NV(a->d / 256, ln_bwd_kernel<NV><<<blocks, LN_WARPS * 32, 0, s>>>(*a));
   if (int rc = check_launch("ln_bwd")) return rc;
   const int width = 3 * a->d;
-  partials_finalize_kernel<<<(width + 255) / 256, 256, 0, s>>>(
+  partials_finalize_kernel<<<(width + FIN_COLS - 1) / FIN_COLS, FIN_COLS * FIN_GROUPS, 0, s>>>(
       a->partials, blocks, width, a->d, static_cast<__nv_bfloat16*>(a->dgamma), static_cast<__nv_bfloat16*>(a->dbeta),
       static_cast<__nv_bfloat16*>(a->dbias));
   return check_launch("ln_bwd finalize");
@@ -431,7 +454,7 @@ extern "C" HSTD_API int hstd_colsum(const void* x, int64_t ld, int M, int N, voi
   dim3 grid((N + 255) / 256, COLSUM_ROWGROUPS);
   colsum_partial_kernel<<<grid, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(x), ld, M, N, partials);
   if (int rc = check_launch("colsum")) return rc;
-  partials_finalize_kernel<<<(N + 255) / 256, 256, 0, s>>>(partials, COLSUM_ROWGROUPS, N, N,
+  partials_finalize_kernel<<<(N + FIN_COLS - 1) / FIN_COLS, FIN_COLS * FIN_GROUPS, 0, s>>>(partials, COLSUM_ROWGROUPS, N, N,
                                                            static_cast<__nv_bfloat16*>(out), nullptr, nullptr);
   return check_launch("colsum finalize");
 }
@@ -531,7 +554,7 @@ extern "C" HSTD_API int hstd_colsum_noalloc(const void* x, int64_t ld, int M, in
   dim3 grid((N + 255) / 256, COLSUM_ROWGROUPS);
   colsum_partial_kernel<<<grid, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(x), ld, M, N, scratch);
   if (int rc = check_launch("colsum_noalloc")) return rc;
-  partials_finalize_kernel<<<(N + 255) / 256, 256, 0, s>>>(scratch, COLSUM_ROWGROUPS, N, N,
+  partials_finalize_kernel<<<(N + FIN_COLS - 1) / FIN_COLS, FIN_COLS * FIN_GROUPS, 0, s>>>(scratch, COLSUM_ROWGROUPS, N, N,
                                                            static_cast<__nv_bfloat16*>(out), nullptr, nullptr);
   return check_launch("colsum_noalloc finalize");
 }
