@@ -1,0 +1,599 @@
+// Fused multi-head attention for sm_100a: softmax(QKᵀ/√dh + key mask) (+ dropout) · V,
+// forward and backward, on tcgen05 tensor cores with S / dP / O / dQ / dK / dV accumulators
+// in TMEM and all operands TMA-loaded straight out of the fused [B*S, 3*d] QKV buffer.
+// The [B,H,S,S] probability tensor is never written to memory (the reference's TF graph
+// materialises it twice: model.fit at scripts/train.py:145).
+//
+// head_dim = 64, S ∈ {128, 256, 384, 512}.  One CTA = 5 warps: warps 0-3 are the softmax /
+// epilogue warps (thread t owns TMEM lane t = one query row), one lane of warp 4 issues
+// every TMA and tcgen05.mma.
+//
+//  forward  (CTA = 128 query rows of one (batch, head)):
+//     S_c = Q·K_cᵀ for all key chunks c (TMEM 128 columns each) → exact row max over all
+//     keys → P_c = exp(S_c·scale − max) (·dropout) written as bf16 into a 128B-swizzled smem
+//     tile → O += P_c·V_c (V read MN-major) → O / rowsum → ctx ; log-sum-exp saved.
+//  backward (CTA = 128 keys of one (batch, head), loop over query tiles i):
+//     S = Q_i·Kᵀ, dP = dO_i·Vᵀ → P = exp(S·scale − lse), dS = P∘(dropout'(dP) − δ) →
+//     dV += Pdᵀ·dO_i, dK += dSᵀ·Q_i (accumulated in TMEM over i), dQ_i = dS·K written as a
+//     per-key-tile partial; a small kernel sums the partials.  The same smem image of a tile
+//     serves as K-major A operand and as MN-major B operand (only the descriptors differ).
+#include <string>
+
+#include "common.cuh"
+#include "device_utils.cuh"
+#include "sm100_ptx.cuh"
+#include "tmap.cuh"
+
+namespace hstd {
+
+constexpr int AT_THREADS = 160;
+constexpr int TILE = 128;        // query rows / keys per tile
+constexpr int DH = 64;           // head dim
+constexpr uint32_t TILE_BYTES = TILE * DH * 2;   // 16 KiB: [128 rows x 128 B]
+constexpr uint32_t P_BYTES = TILE * TILE * 2;    // 32 KiB: two 64-column swizzle atoms
+constexpr float LOG2E = 1.4426950408889634f;
+
+struct AttnParams {
+  __nv_bfloat16* ctx;          // fwd out [B,S,H*64]
+  float* lse;                  // [B,H,S] natural-log log-sum-exp of the scaled scores
+  const float* delta;          // bwd [B,H,S] rowsum(dO ∘ O)
+  __nv_bfloat16* dqkv;         // bwd out [B*S, 3*d] (K and V slots written here)
+  __nv_bfloat16* dq_part;      // bwd out [S/128][B*S][d] partial dQ per key tile
+  const int32_t* key_mask;     // [B,S] 1 = attend
+  const StepState* st;
+  float p_drop;
+  uint32_t site;
+  int B, H, S;
+  float scale;
+};
+
+// byte offset of 16-byte chunk `chunk` (0..7) of row `row` inside a [128 x 128B] swizzled atom
+__device__ __forceinline__ uint32_t swz(uint32_t row, uint32_t chunk) { return row * 128u + ((chunk ^ (row & 7u)) << 4); }
+
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// Writes 32 consecutive columns [col0, col0+32) of row `row` (bf16) into a K-major SW128
+// tile made of 64-column atoms of 16 KiB each.
+__device__ __forceinline__ void store_row32(uint8_t* tile, uint32_t row, uint32_t col0, const float (&v)[32]) {
+  uint8_t* atom = tile + (col0 >> 6) * TILE_BYTES;
+  const uint32_t chunk0 = (col0 & 63u) >> 3;
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    uint4 o = make_uint4(pack_bf16x2(v[8 * c], v[8 * c + 1]), pack_bf16x2(v[8 * c + 2], v[8 * c + 3]),
+                         pack_bf16x2(v[8 * c + 4], v[8 * c + 5]), pack_bf16x2(v[8 * c + 6], v[8 * c + 7]));
+    *reinterpret_cast<uint4*>(atom + swz(row, chunk0 + c)) = o;
+  }
+}
+
+// ============================================================================ forward
+template <int NC>
+__global__ void __launch_bounds__(AT_THREADS, 1)
+attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
+                const __grid_constant__ CUtensorMap tm_v, const AttnParams p) {
+  constexpr uint32_t TMEM_COLS = NC == 1 ? 128 : (NC == 2 ? 256 : 512);
+  constexpr uint32_t IDESC_S = make_idesc_bf16(TILE, TILE, false, false);
+  constexpr uint32_t IDESC_O = make_idesc_bf16(TILE, DH, false, true);
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;
+  uint8_t* sK = sQ + TILE_BYTES;
+  uint8_t* sV = sK + NC * TILE_BYTES;
+  uint8_t* sP = sV + NC * TILE_BYTES;  // 2 buffers
+  float* sBias = reinterpret_cast<float*>(sP + 2 * P_BYTES);  // [NC*128]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sBias + NC * TILE);
+  uint64_t* bar_qk = bars;
+  uint64_t* bar_v = bars + 1;
+  uint64_t* bar_o = bars + 2;
+  uint64_t* bar_s = bars + 3;            // [NC]
+  uint64_t* bar_p = bar_s + NC;          // [2]
+  uint64_t* bar_pfree = bar_p + 2;       // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_pfree + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  const int Sk = NC * TILE;
+
+  if (warp == 4) {
+    if (lane == 0) {
+      tma_prefetch_desc(&tm_q); tma_prefetch_desc(&tm_k); tma_prefetch_desc(&tm_v);
+      mbar_init(bar_qk, 1); mbar_init(bar_v, 1); mbar_init(bar_o, 1);
+      for (int c = 0; c < NC; ++c) mbar_init(&bar_s[c], 1);
+      for (int i = 0; i < 2; ++i) { mbar_init(&bar_p[i], 128); mbar_init(&bar_pfree[i], 1); }
+      fence_mbar_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, TMEM_COLS);
+    tmem_relinquish();
+  } else {
+    for (int i = threadIdx.x; i < Sk; i += 128) sBias[i] = p.key_mask[int64_t(b) * p.S + i] ? 0.f : -INFINITY;
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 4) {
+    if (lane == 0) {
+      mbar_expect_tx(bar_qk, (1 + NC) * TILE_BYTES);
+      tma_load_4d(sQ, &tm_q, bar_qk, 0, qt * TILE, h, b);
+      for (int c = 0; c < NC; ++c) tma_load_4d(sK + c * TILE_BYTES, &tm_k, bar_qk, 0, c * TILE, h, b);
+      mbar_expect_tx(bar_v, NC * TILE_BYTES);
+      for (int c = 0; c < NC; ++c) tma_load_4d(sV + c * TILE_BYTES, &tm_v, bar_v, 0, c * TILE, h, b);
+      mbar_wait(bar_qk, 0);
+      tc_fence_after();
+      const uint32_t q_addr = smem_u32(sQ);
+      for (int c = 0; c < NC; ++c) {
+        const uint32_t k_addr = smem_u32(sK + c * TILE_BYTES);
+#pragma unroll
+        for (int k = 0; k < DH / 16; ++k)
+          umma_bf16(tmem + c * TILE, make_smem_desc_sw128(q_addr + k * 32, 16, 1024),
+                    make_smem_desc_sw128(k_addr + k * 32, 16, 1024), IDESC_S, k > 0);
+        umma_commit(&bar_s[c]);
+      }
+      mbar_wait(bar_v, 0);
+      for (int c = 0; c < NC; ++c) {
+        const int buf = c & 1;
+        mbar_wait(&bar_p[buf], (c >> 1) & 1);
+        tc_fence_after();
+        const uint32_t p_addr = smem_u32(sP + buf * P_BYTES);
+        const uint32_t v_addr = smem_u32(sV + c * TILE_BYTES);
+#pragma unroll
+        for (int k = 0; k < TILE / 16; ++k)
+          umma_bf16(tmem, make_smem_desc_sw128(p_addr + (k >> 2) * TILE_BYTES + (k & 3) * 32, 16, 1024),
+                    make_smem_desc_sw128(v_addr + k * 2048, TILE_BYTES, 1024), IDESC_O, (c > 0 || k > 0));
+        umma_commit(&bar_pfree[buf]);
+      }
+      umma_commit(bar_o);
+    }
+  } else {
+    const uint32_t row = threadIdx.x;                       // 0..127 = TMEM lane
+    const uint32_t t_row = tmem + ((uint32_t(warp) * 32u) << 16);
+    const float scale2 = p.scale * LOG2E;
+    // ---- pass 1: exact row maximum over every key
+    float mx = -INFINITY;
+    for (int c = 0; c < NC; ++c) {
+      mbar_wait(&bar_s[c], 0);
+      tc_fence_after();
+#pragma unroll 1
+      for (int sb = 0; sb < 4; ++sb) {
+        uint32_t v[32];
+        tmem_ld_32x32(t_row + c * TILE + sb * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(v[j]) + sBias[c * TILE + sb * 32 + j]);
+      }
+    }
+    const float m2 = (mx == -INFINITY) ? 0.f : mx * scale2;
+    // ---- pass 2: probabilities -> smem (bf16), running row sum
+    const Dropout dr = make_dropout(p.st, p.p_drop, p.site);
+    const uint64_t row_base = (uint64_t(b) * p.H + h) * p.S + uint64_t(qt) * TILE + row;  // global score row
+    float l = 0.f;
+    for (int c = 0; c < NC; ++c) {
+      const int buf = c & 1;
+      if (c >= 2) mbar_wait(&bar_pfree[buf], ((c - 2) >> 1) & 1);
+      uint8_t* pt = sP + buf * P_BYTES;
+#pragma unroll 1
+      for (int sb = 0; sb < 4; ++sb) {
+        uint32_t v[32];
+        tmem_ld_32x32(t_row + c * TILE + sb * 32, v);
+        tmem_ld_wait();
+        float f[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const float s = __uint_as_float(v[j]) + sBias[c * TILE + sb * 32 + j];
+          f[j] = fast_exp2(s * scale2 - m2);
+          l += f[j];
+        }
+        if (dr.active()) {
+          const uint64_t e0 = row_base * Sk + c * TILE + sb * 32;
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            float m[8];
+            dropout_mask8(dr, (e0 >> 3) + g, m);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) f[8 * g + j] *= m[j];
+          }
+        }
+        store_row32(pt, row, sb * 32, f);
+      }
+      tc_fence_before();
+      fence_proxy_async_smem();
+      mbar_arrive(&bar_p[buf]);
+    }
+    // ---- epilogue: O / l -> ctx, log-sum-exp
+    mbar_wait(bar_o, 0);
+    tc_fence_after();
+    const float inv_l = l > 0.f ? 1.f / l : 0.f;
+    __nv_bfloat16* out = p.ctx + (int64_t(b) * p.S + qt * TILE + row) * (int64_t(p.H) * DH) + h * DH;
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      uint32_t v[32];
+      tmem_ld_32x32(t_row + half * 32, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        uint4 o = make_uint4(pack_bf16x2(__uint_as_float(v[8 * c]) * inv_l, __uint_as_float(v[8 * c + 1]) * inv_l),
+                             pack_bf16x2(__uint_as_float(v[8 * c + 2]) * inv_l, __uint_as_float(v[8 * c + 3]) * inv_l),
+                             pack_bf16x2(__uint_as_float(v[8 * c + 4]) * inv_l, __uint_as_float(v[8 * c + 5]) * inv_l),
+                             pack_bf16x2(__uint_as_float(v[8 * c + 6]) * inv_l, __uint_as_float(v[8 * c + 7]) * inv_l));
+        *reinterpret_cast<uint4*>(out + half * 32 + c * 8) = o;
+      }
+    }
+    if (p.lse) p.lse[row_base] = (mx == -INFINITY ? 0.f : mx * p.scale) + __logf(fmaxf(l, 1e-30f));
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) {
+    tc_fence_after();
+    tmem_dealloc(tmem, TMEM_COLS);
+  }
+}
+
+// ============================================================================ backward
+// delta[b,h,q] = sum_j dO[b,q,h,j] * O[b,q,h,j]; one warp per (b,q) row of width H*64.
+__global__ void __launch_bounds__(256) attn_delta_kernel(const __nv_bfloat16* __restrict__ dO,
+                                                         const __nv_bfloat16* __restrict__ O, float* __restrict__ delta,
+                                                         int B, int S, int H) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= B * S) return;
+  const int b = warp / S, q = warp - b * S;
+  const int d = H * DH;
+  for (int col = lane * 8; col < d; col += 256) {
+    float x[8], y[8];
+    load8(dO + int64_t(warp) * d + col, x);
+    load8(O + int64_t(warp) * d + col, y);
+    float s = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s += x[j] * y[j];
+    s += __shfl_xor_sync(0xffffffffu, s, 1);
+    s += __shfl_xor_sync(0xffffffffu, s, 2);
+    s += __shfl_xor_sync(0xffffffffu, s, 4);
+    if ((lane & 7) == 0) delta[(int64_t(b) * H + col / DH) * S + q] = s;
+  }
+}
+
+template <int NQ>
+__global__ void __launch_bounds__(AT_THREADS, 1)
+attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
+                const __grid_constant__ CUtensorMap tm_v, const __grid_constant__ CUtensorMap tm_do,
+                const AttnParams p) {
+  constexpr uint32_t TMEM_COLS = 512;
+  constexpr uint32_t C_S = 0, C_DP = 128, C_DV = 256, C_DK = 320, C_DQ = 384;
+  constexpr uint32_t IDESC_S = make_idesc_bf16(TILE, TILE, false, false);   // Q·Kᵀ, dO·Vᵀ
+  constexpr uint32_t IDESC_T = make_idesc_bf16(TILE, DH, true, true);       // Pdᵀ·dO, dSᵀ·Q
+  constexpr uint32_t IDESC_Q = make_idesc_bf16(TILE, DH, false, true);      // dS·K
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sK = smem;
+  uint8_t* sV = sK + TILE_BYTES;
+  uint8_t* sQ = sV + TILE_BYTES;        // 2 buffers
+  uint8_t* sDO = sQ + 2 * TILE_BYTES;   // 2 buffers
+  uint8_t* sPd = sDO + 2 * TILE_BYTES;  // 32 KiB
+  uint8_t* sDS = sPd + P_BYTES;         // 32 KiB
+  float* sBias = reinterpret_cast<float*>(sDS + P_BYTES);  // [128]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sBias + TILE);
+  uint64_t* bar_kv = bars;
+  uint64_t* bar_q = bars + 1;       // [2]
+  uint64_t* bar_sdp = bars + 3;
+  uint64_t* bar_pds = bars + 4;
+  uint64_t* bar_dq = bars + 5;
+  uint64_t* bar_dqread = bars + 6;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 7);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int kt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  const int S = p.S;
+
+  if (warp == 4) {
+    if (lane == 0) {
+      tma_prefetch_desc(&tm_q); tma_prefetch_desc(&tm_k); tma_prefetch_desc(&tm_v); tma_prefetch_desc(&tm_do);
+      mbar_init(bar_kv, 1); mbar_init(&bar_q[0], 1); mbar_init(&bar_q[1], 1);
+      mbar_init(bar_sdp, 1); mbar_init(bar_pds, 128); mbar_init(bar_dq, 1); mbar_init(bar_dqread, 128);
+      fence_mbar_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, TMEM_COLS);
+    tmem_relinquish();
+  } else {
+    sBias[threadIdx.x] = p.key_mask[int64_t(b) * S + kt * TILE + threadIdx.x] ? 0.f : -INFINITY;
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 4) {
+    if (lane == 0) {
+      mbar_expect_tx(bar_kv, 2 * TILE_BYTES);
+      tma_load_4d(sK, &tm_k, bar_kv, 0, kt * TILE, h, b);
+      tma_load_4d(sV, &tm_v, bar_kv, 0, kt * TILE, h, b);
+      for (int i = 0; i < 2 && i < NQ; ++i) {
+        mbar_expect_tx(&bar_q[i], 2 * TILE_BYTES);
+        tma_load_4d(sQ + i * TILE_BYTES, &tm_q, &bar_q[i], 0, i * TILE, h, b);
+        tma_load_4d(sDO + i * TILE_BYTES, &tm_do, &bar_q[i], 0, i * TILE, h, b);
+      }
+      mbar_wait(bar_kv, 0);
+      const uint32_t k_addr = smem_u32(sK), v_addr = smem_u32(sV);
+      const uint32_t pd_addr = smem_u32(sPd), ds_addr = smem_u32(sDS);
+      for (int i = 0; i < NQ; ++i) {
+        const int buf = i & 1;
+        mbar_wait(&bar_q[buf], (i >> 1) & 1);
+        tc_fence_after();
+        const uint32_t q_addr = smem_u32(sQ + buf * TILE_BYTES), do_addr = smem_u32(sDO + buf * TILE_BYTES);
+#pragma unroll
+        for (int k = 0; k < DH / 16; ++k)
+          umma_bf16(tmem + C_S, make_smem_desc_sw128(q_addr + k * 32, 16, 1024),
+                    make_smem_desc_sw128(k_addr + k * 32, 16, 1024), IDESC_S, k > 0);
+#pragma unroll
+        for (int k = 0; k < DH / 16; ++k)
+          umma_bf16(tmem + C_DP, make_smem_desc_sw128(do_addr + k * 32, 16, 1024),
+                    make_smem_desc_sw128(v_addr + k * 32, 16, 1024), IDESC_S, k > 0);
+        umma_commit(bar_sdp);
+        mbar_wait(bar_pds, i & 1);
+        tc_fence_after();
+        if (i > 0) {
+          mbar_wait(bar_dqread, (i - 1) & 1);
+          tc_fence_after();
+        }
+        // reduction over the 128 query rows of this tile: 8 k-steps of 16 rows = 2048 B each
+#pragma unroll
+        for (int k = 0; k < TILE / 16; ++k)
+          umma_bf16(tmem + C_DV, make_smem_desc_sw128(pd_addr + k * 2048, TILE_BYTES, 1024),
+                    make_smem_desc_sw128(do_addr + k * 2048, TILE_BYTES, 1024), IDESC_T, (i > 0 || k > 0));
+#pragma unroll
+        for (int k = 0; k < TILE / 16; ++k)
+          umma_bf16(tmem + C_DK, make_smem_desc_sw128(ds_addr + k * 2048, TILE_BYTES, 1024),
+                    make_smem_desc_sw128(q_addr + k * 2048, TILE_BYTES, 1024), IDESC_T, (i > 0 || k > 0));
+        // dQ_i = dS · K : reduction over the 128 keys (dS K-major: 4 k-steps per 64-key atom)
+#pragma unroll
+        for (int k = 0; k < TILE / 16; ++k)
+          umma_bf16(tmem + C_DQ, make_smem_desc_sw128(ds_addr + (k >> 2) * TILE_BYTES + (k & 3) * 32, 16, 1024),
+                    make_smem_desc_sw128(k_addr + k * 2048, TILE_BYTES, 1024), IDESC_Q, k > 0);
+        umma_commit(bar_dq);
+        mbar_wait(bar_dq, i & 1);  // tiles Q/dO[buf], Pd, dS are free again
+        if (i + 2 < NQ) {
+          mbar_expect_tx(&bar_q[buf], 2 * TILE_BYTES);
+          tma_load_4d(sQ + buf * TILE_BYTES, &tm_q, &bar_q[buf], 0, (i + 2) * TILE, h, b);
+          tma_load_4d(sDO + buf * TILE_BYTES, &tm_do, &bar_q[buf], 0, (i + 2) * TILE, h, b);
+        }
+      }
+    }
+  } else {
+    const uint32_t row = threadIdx.x;
+    const uint32_t t_row = tmem + ((uint32_t(warp) * 32u) << 16);
+    const float scale2 = p.scale * LOG2E;
+    const Dropout dr = make_dropout(p.st, p.p_drop, p.site);
+    const int d = p.H * DH;
+    for (int i = 0; i < NQ; ++i) {
+      const uint64_t srow = (uint64_t(b) * p.H + h) * S + uint64_t(i) * TILE + row;  // global score row
+      const float lse2 = p.lse[srow] * LOG2E;
+      const float dl = p.delta[srow];
+      mbar_wait(bar_sdp, i & 1);
+      tc_fence_after();
+#pragma unroll 1
+      for (int sb = 0; sb < 4; ++sb) {
+        uint32_t vs[32], vd[32];
+        tmem_ld_32x32(t_row + C_S + sb * 32, vs);
+        tmem_ld_32x32(t_row + C_DP + sb * 32, vd);
+        tmem_ld_wait();
+        float pd[32], ds[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const float s = __uint_as_float(vs[j]) + sBias[sb * 32 + j];
+          pd[j] = fast_exp2(s * scale2 - lse2);  // P (masked keys -> 0)
+          ds[j] = __uint_as_float(vd[j]);        // dPd
+        }
+        if (dr.active()) {
+          const uint64_t e0 = srow * S + kt * TILE + sb * 32;
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            float m[8];
+            dropout_mask8(dr, (e0 >> 3) + g, m);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float pj = pd[8 * g + j];
+              ds[8 * g + j] = pj * (ds[8 * g + j] * m[j] - dl);
+              pd[8 * g + j] = pj * m[j];
+            }
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) ds[j] = pd[j] * (ds[j] - dl);
+        }
+        store_row32(sPd, row, sb * 32, pd);
+        store_row32(sDS, row, sb * 32, ds);
+      }
+      tc_fence_before();
+      fence_proxy_async_smem();
+      mbar_arrive(bar_pds);
+      // dQ partial of this (query tile, key tile)
+      mbar_wait(bar_dq, i & 1);
+      tc_fence_after();
+      __nv_bfloat16* out = p.dq_part + (int64_t(kt) * p.B * S + int64_t(b) * S + i * TILE + row) * d + h * DH;
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        uint32_t v[32];
+        tmem_ld_32x32(t_row + C_DQ + half * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          uint4 o = make_uint4(
+              pack_bf16x2(__uint_as_float(v[8 * c]) * p.scale, __uint_as_float(v[8 * c + 1]) * p.scale),
+              pack_bf16x2(__uint_as_float(v[8 * c + 2]) * p.scale, __uint_as_float(v[8 * c + 3]) * p.scale),
+              pack_bf16x2(__uint_as_float(v[8 * c + 4]) * p.scale, __uint_as_float(v[8 * c + 5]) * p.scale),
+              pack_bf16x2(__uint_as_float(v[8 * c + 6]) * p.scale, __uint_as_float(v[8 * c + 7]) * p.scale));
+          *reinterpret_cast<uint4*>(out + half * 32 + c * 8) = o;
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(bar_dqread);
+    }
+    // dK (x scale) and dV of this key tile; the last bar_dq wait above covered all MMAs
+    __nv_bfloat16* orow = p.dqkv + (int64_t(b) * S + kt * TILE + row) * (3 * int64_t(d)) + h * DH;
+#pragma unroll
+    for (int which = 0; which < 2; ++which) {  // 0: dK -> slot 1, 1: dV -> slot 2
+      const float sc = which == 0 ? p.scale : 1.f;
+      __nv_bfloat16* out = orow + (which + 1) * int64_t(d);
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        uint32_t v[32];
+        tmem_ld_32x32(t_row + (which == 0 ? C_DK : C_DV) + half * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          uint4 o = make_uint4(pack_bf16x2(__uint_as_float(v[8 * c]) * sc, __uint_as_float(v[8 * c + 1]) * sc),
+                               pack_bf16x2(__uint_as_float(v[8 * c + 2]) * sc, __uint_as_float(v[8 * c + 3]) * sc),
+                               pack_bf16x2(__uint_as_float(v[8 * c + 4]) * sc, __uint_as_float(v[8 * c + 5]) * sc),
+                               pack_bf16x2(__uint_as_float(v[8 * c + 6]) * sc, __uint_as_float(v[8 * c + 7]) * sc));
+          *reinterpret_cast<uint4*>(out + half * 32 + c * 8) = o;
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) {
+    tc_fence_after();
+    tmem_dealloc(tmem, TMEM_COLS);
+  }
+}
+
+// dqkv[:, 0:d] = sum over key tiles of dq_part
+__global__ void __launch_bounds__(256) attn_dq_reduce_kernel(const __nv_bfloat16* __restrict__ part,
+                                                             __nv_bfloat16* __restrict__ dqkv, int64_t M, int d,
+                                                             int nparts) {
+  const int64_t nvec = M * d / 8;
+  for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < nvec; i += int64_t(gridDim.x) * blockDim.x) {
+    float acc[8];
+    load8(part + i * 8, acc);
+    for (int k = 1; k < nparts; ++k) {
+      float t[8];
+      load8(part + (int64_t(k) * M * d) + i * 8, t);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += t[j];
+    }
+    const int64_t e = i * 8;
+    const int64_t row = e / d;
+    const int col = int(e - row * d);
+    store8(dqkv + row * (3 * int64_t(d)) + col, acc);
+  }
+}
+
+static size_t fwd_smem(int nc) { return 1024 + size_t(1 + 2 * nc) * TILE_BYTES + 2 * P_BYTES + nc * TILE * 4 + 256; }
+static size_t bwd_smem() { return 1024 + 6 * size_t(TILE_BYTES) + 2 * P_BYTES + TILE * 4 + 256; }
+
+template <typename Kern>
+static int set_smem(Kern k, size_t bytes) {
+  cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(bytes));
+  if (e != cudaSuccess) return set_error(-5, std::string("attention cudaFuncSetAttribute: ") + cudaGetErrorString(e));
+  return 0;
+}
+
+static int check_shape(int B, int H, int S) {
+  if (S % TILE != 0 || S < TILE || S > 4 * TILE) return set_error(-1, "attention: S must be 128, 256, 384 or 512");
+  if (B <= 0 || H <= 0) return set_error(-1, "attention: empty problem");
+  return 0;
+}
+
+}  // namespace hstd
+
+using namespace hstd;
+
+extern "C" HSTD_API int hstd_attn_fwd(const void* qkv, void* ctx, float* lse, const int32_t* key_mask, int B, int H,
+                                      int S, float scale, float p_drop, uint32_t site, const hstd_step_state* st,
+                                      void* stream) {
+  if (int rc = check_shape(B, H, S)) return rc;
+  const int64_t d = int64_t(H) * DH;
+  const __nv_bfloat16* base = static_cast<const __nv_bfloat16*>(qkv);
+  CUtensorMap tq, tk, tv;
+  // dims {dh, S (row stride 3d), H (stride dh), B (stride S*3d)}; box {64, 128}
+  if (int rc = get_tmap(&tq, base, DH, S, H, B, 3 * d, DH, S * 3 * d, TILE)) return rc;
+  if (int rc = get_tmap(&tk, base + d, DH, S, H, B, 3 * d, DH, S * 3 * d, TILE)) return rc;
+  if (int rc = get_tmap(&tv, base + 2 * d, DH, S, H, B, 3 * d, DH, S * 3 * d, TILE)) return rc;
+  AttnParams p{};
+  p.ctx = static_cast<__nv_bfloat16*>(ctx);
+  p.lse = lse;
+  p.key_mask = key_mask;
+  p.st = st; p.p_drop = p_drop; p.site = site;
+  p.B = B; p.H = H; p.S = S; p.scale = scale;
+  const int nc = S / TILE;
+  dim3 grid(nc, H, B);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  static bool configured[5] = {false, false, false, false, false};
+#define HSTD_ATTN_FWD(NC_)                                                        \
+  case NC_: {                                                                     \
+    if (!configured[NC_]) {                                                       \
+      if (int rc = set_smem(attn_fwd_kernel<NC_>, fwd_smem(NC_))) return rc;      \
+      configured[NC_] = true;                                                     \
+    }                                                                             \
+    attn_fwd_kernel<NC_><<<grid, AT_THREADS, fwd_smem(NC_), s>>>(tq, tk, tv, p);  \
+    break;                                                                        \
+  }
+  switch (nc) {
+    HSTD_ATTN_FWD(1) HSTD_ATTN_FWD(2) HSTD_ATTN_FWD(3) HSTD_ATTN_FWD(4)
+    default: return set_error(-1, "attention: unsupported S");
+  }
+#undef HSTD_ATTN_FWD
+  return check_launch("attn_fwd");
+}
+
+extern "C" HSTD_API int64_t hstd_attn_bwd_workspace_bytes(int B, int H, int S) {
+  // delta [B,H,S] fp32 + dq partials [S/128][B*S][H*64] bf16
+  return int64_t(B) * H * S * 4 + int64_t(S / TILE) * B * S * H * DH * 2;
+}
+
+extern "C" HSTD_API int hstd_attn_bwd(const void* qkv, const void* ctx, const void* dctx, const float* lse,
+                                      const int32_t* key_mask, void* dqkv, void* workspace, int B, int H, int S,
+                                      float scale, float p_drop, uint32_t site, const hstd_step_state* st,
+                                      void* stream) {
+  if (int rc = check_shape(B, H, S)) return rc;
+  if (!workspace) return set_error(-1, "attn_bwd: workspace required");
+  const int64_t d = int64_t(H) * DH;
+  const int64_t M = int64_t(B) * S;
+  float* delta = static_cast<float*>(workspace);
+  __nv_bfloat16* dq_part = reinterpret_cast<__nv_bfloat16*>(static_cast<uint8_t*>(workspace) + int64_t(B) * H * S * 4);
+  const __nv_bfloat16* base = static_cast<const __nv_bfloat16*>(qkv);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  attn_delta_kernel<<<unsigned((M * 32 + 255) / 256), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(dctx),
+                                                                    static_cast<const __nv_bfloat16*>(ctx), delta, B, S, H);
+  if (int rc = check_launch("attn_delta")) return rc;
+  CUtensorMap tq, tk, tv, tdo;
+  if (int rc = get_tmap(&tq, base, DH, S, H, B, 3 * d, DH, S * 3 * d, TILE)) return rc;
+  if (int rc = get_tmap(&tk, base + d, DH, S, H, B, 3 * d, DH, S * 3 * d, TILE)) return rc;
+  if (int rc = get_tmap(&tv, base + 2 * d, DH, S, H, B, 3 * d, DH, S * 3 * d, TILE)) return rc;
+  if (int rc = get_tmap(&tdo, dctx, DH, S, H, B, d, DH, S * d, TILE)) return rc;
+  AttnParams p{};
+  p.lse = const_cast<float*>(lse);
+  p.delta = delta;
+  p.dqkv = static_cast<__nv_bfloat16*>(dqkv);
+  p.dq_part = dq_part;
+  p.key_mask = key_mask;
+  p.st = st; p.p_drop = p_drop; p.site = site;
+  p.B = B; p.H = H; p.S = S; p.scale = scale;
+  const int nq = S / TILE;
+  dim3 grid(nq, H, B);
+  static bool configured[5] = {false, false, false, false, false};
+#define HSTD_ATTN_BWD(NQ_)                                                             \
+  case NQ_: {                                                                          \
+    if (!configured[NQ_]) {                                                            \
+      if (int rc = set_smem(attn_bwd_kernel<NQ_>, bwd_smem())) return rc;              \
+      configured[NQ_] = true;                                                          \
+    }                                                                                  \
+    attn_bwd_kernel<NQ_><<<grid, AT_THREADS, bwd_smem(), s>>>(tq, tk, tv, tdo, p);     \
+    break;                                                                             \
+  }
+  switch (nq) {
+    HSTD_ATTN_BWD(1) HSTD_ATTN_BWD(2) HSTD_ATTN_BWD(3) HSTD_ATTN_BWD(4)
+    default: return set_error(-1, "attention: unsupported S");
+  }
+#undef HSTD_ATTN_BWD
+  if (int rc = check_launch("attn_bwd")) return rc;
+  int blocks = int((M * d / 8 + 255) / 256);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  attn_dq_reduce_kernel<<<blocks, 256, 0, s>>>(dq_part, static_cast<__nv_bfloat16*>(dqkv), M, int(d), nq);
+  return check_launch("attn_dq_reduce");
+}

@@ -89,7 +89,8 @@ class EngineBackend:
     name = "engine"
 
     def __init__(self, cfg: EncoderConfig, device: torch.device, seed: int = 42, bucket_mb: float = 32.0,
-                 comm_mode: str = "p2p", use_cuda_graph: bool = True, overlap: bool = True):
+                 comm_mode: str = "p2p", use_cuda_graph: bool = True, overlap: bool = True,
+                 fused_attention: bool = True):
         if device.type != "cuda":
             raise RuntimeError("EngineBackend needs a CUDA device")
         _lib.load()  # fail loudly if libhstd_b200.so is missing: no silent eager fallback
@@ -100,6 +101,7 @@ class EngineBackend:
         self.cfg, self.device = cfg, device
         self.use_cuda_graph = use_cuda_graph
         self.bucket_mb, self.comm_mode, self.overlap = bucket_mb, comm_mode, overlap
+        self.fused_attention = fused_attention
         self.seed = seed
         self.world, self.rank = comm.size(), comm.rank()
 
@@ -250,6 +252,27 @@ class EngineBackend:
             self._gemm_op(plan, A=dy, B=w, C=dx, lda=N, ldb=Kd, ldc=Kd, M=M, N=Kd, K=N, b_t=True, epilogue=epilogue,
                           aux=aux, ldaux=ldaux)
 
+    def _attention_bwd_unfused(self, plan, i, qkv, Pd, P, dP, dctx, dqkv, B, S, H, dh, d, scale, p_att, st, op):
+        """Attention backward as four batched GEMMs + a softmax-backward kernel (materialised P)."""
+        hb = dict(nb0=H, nb1=B)
+        q_s = dict(bs0=dh, bs1=S * 3 * d)  # strides of a Q/K/V/dQ/dK/dV slice inside [M,3d]
+        # dPd = dctx · Vᵀ
+        self._gemm_op(plan, A=dctx, B=(qkv[i], 2 * d), C=dP, lda=d, ldb=3 * d, ldc=S, a_bs0=dh, a_bs1=S * d,
+                      b_bs0=q_s["bs0"], b_bs1=q_s["bs1"], c_bs0=S * S, c_bs1=H * S * S, M=S, N=S, K=dh, **hb)
+        # dV = Pdᵀ · dctx
+        self._gemm_op(plan, A=Pd[i], B=dctx, C=(dqkv, 2 * d), lda=S, ldb=d, ldc=3 * d, a_bs0=S * S, a_bs1=H * S * S,
+                      b_bs0=dh, b_bs1=S * d, c_bs0=q_s["bs0"], c_bs1=q_s["bs1"], M=S, N=dh, K=S, a_t=True, b_t=True,
+                      **hb)
+        op(lambda i=i: K.softmax_bwd(P[i], dP, p_drop=p_att, site=i * 8 + 1, state=st))
+        # dQ = scale * dS · K
+        self._gemm_op(plan, A=dP, B=(qkv[i], d), C=dqkv, lda=S, ldb=3 * d, ldc=3 * d, a_bs0=S * S, a_bs1=H * S * S,
+                      b_bs0=q_s["bs0"], b_bs1=q_s["bs1"], c_bs0=q_s["bs0"], c_bs1=q_s["bs1"], M=S, N=dh, K=S,
+                      b_t=True, alpha=scale, **hb)
+        # dK = scale * dSᵀ · Q
+        self._gemm_op(plan, A=dP, B=qkv[i], C=(dqkv, d), lda=S, ldb=3 * d, ldc=3 * d, a_bs0=S * S, a_bs1=H * S * S,
+                      b_bs0=q_s["bs0"], b_bs1=q_s["bs1"], c_bs0=q_s["bs0"], c_bs1=q_s["bs1"], M=S, N=dh, K=S,
+                      a_t=True, b_t=True, alpha=scale, **hb)
+
     def build_plan(self, B: int, S: int, train: bool) -> Plan:
         cfg = self.cfg
         if S % 128 or S > 512:
@@ -277,8 +300,13 @@ class EngineBackend:
         if not train:
             xa, xb = self._buf(plan, "xa", (M, d)), self._buf(plan, "xb", (M, d))
         qkv, ctx = lb("qkv", (M, 3 * d)), lb("ctx", (M, d))
-        P = lb("P", (B, H, S, S))
-        Pd = lb("Pd", (B, H, S, S)) if p_att > 0 else P
+        fused = self.fused_attention
+        if fused:
+            P = Pd = None
+            lse = lb("lse", (B, H, S), torch.float32)
+        else:
+            P = lb("P", (B, H, S, S))
+            Pd = lb("Pd", (B, H, S, S)) if p_att > 0 else P
         r1, h1, r2 = lb("r1", (M, d)), lb("h1", (M, d)), lb("r2", (M, d))
         u, f = lb("u", (M, F)), lb("f", (M, F))
         f32 = torch.float32
@@ -314,16 +342,20 @@ class EngineBackend:
             pfx = f"layers.{i}."
             x, xn = X(i), X(i + 1)
             self._linear_fwd(plan, x, pfx + "qkv", qkv[j], M)
-            # scores = scale * Q Kᵀ  per (head, batch)
-            self._gemm_op(plan, A=qkv[j], B=(qkv[j], d), C=P[j], lda=3 * d, ldb=3 * d, ldc=S, a_bs0=dh, a_bs1=S * 3 * d,
-                          b_bs0=dh, b_bs1=S * 3 * d, c_bs0=S * S, c_bs1=H * S * S, M=S, N=S, K=dh, nb0=H, nb1=B,
-                          alpha=scale)
-            op(lambda j=j, i=i: K.softmax_fwd(P[j], mask, pd=(Pd[j] if p_att > 0 else None), p_drop=p_att,
-                                              site=i * 8 + 1, state=sref))
-            # ctx = Pd · V   (V read MN-major straight out of the fused QKV buffer)
-            self._gemm_op(plan, A=Pd[j], B=(qkv[j], 2 * d), C=ctx[j], lda=S, ldb=3 * d, ldc=d, a_bs0=S * S,
-                          a_bs1=H * S * S, b_bs0=dh, b_bs1=S * 3 * d, c_bs0=dh, c_bs1=S * d, M=S, N=dh, K=S, nb0=H,
-                          nb1=B, b_t=True)
+            if fused:
+                op(lambda j=j, i=i: K.attn_fwd(qkv[j], ctx[j], lse[j], mask, B, H, S, scale, p_drop=p_att,
+                                               site=i * 8 + 1, state=sref))
+            else:
+                # scores = scale * Q Kᵀ  per (head, batch)
+                self._gemm_op(plan, A=qkv[j], B=(qkv[j], d), C=P[j], lda=3 * d, ldb=3 * d, ldc=S, a_bs0=dh,
+                              a_bs1=S * 3 * d, b_bs0=dh, b_bs1=S * 3 * d, c_bs0=S * S, c_bs1=H * S * S, M=S, N=S, K=dh,
+                              nb0=H, nb1=B, alpha=scale)
+                op(lambda j=j, i=i: K.softmax_fwd(P[j], mask, pd=(Pd[j] if p_att > 0 else None), p_drop=p_att,
+                                                  site=i * 8 + 1, state=sref))
+                # ctx = Pd · V   (V read MN-major straight out of the fused QKV buffer)
+                self._gemm_op(plan, A=Pd[j], B=(qkv[j], 2 * d), C=ctx[j], lda=S, ldb=3 * d, ldc=d, a_bs0=S * S,
+                              a_bs1=H * S * S, b_bs0=dh, b_bs1=S * 3 * d, c_bs0=dh, c_bs1=S * d, M=S, N=dh, K=S,
+                              nb0=H, nb1=B, b_t=True)
             self._linear_fwd(plan, ctx[j], pfx + "out", r1[j], M)
             op(lambda j=j, i=i, x=x: K.ln_fwd(a=r1[j], resid=x, pre=r1[j], y=h1[j], mean=mean1[j], rstd=rstd1[j],
                                               gamma=self.W(f"layers.{i}.ln1.weight"), beta=self.W(f"layers.{i}.ln1.bias"),
@@ -356,7 +388,8 @@ class EngineBackend:
         bufA, bufB, bufC = (self._buf(plan, n, (M, d)) for n in ("gA", "gB", "gC"))
         dctx = self._buf(plan, "dctx", (M, d))
         du = self._buf(plan, "du", (M, F))
-        dP = self._buf(plan, "dP", (B, H, S, S))
+        dP = None if fused else self._buf(plan, "dP", (B, H, S, S))
+        attn_ws = self._shared("attn_ws", K.attn_bwd_workspace_bytes(B, H, S), torch.uint8) if fused else None
         dqkv = self._buf(plan, "dqkv", (M, 3 * d))
         lnp = self._shared("ln_partials", K.ln_bwd_partials_floats(d))
         self.dp.begin_backward(plan)
@@ -386,25 +419,11 @@ class EngineBackend:
                                              p_in=p_attn_out, site_in=i * 8 + 2), 2)
             da = da1 if da1 is not None else bufA
             self._linear_bwd(plan, da, ctx[i], pfx + "out", dctx, M, bias_grad=False)
-            # attention backward (all batched over (head, batch))
-            hb = dict(nb0=H, nb1=B)
-            q_s = dict(bs0=dh, bs1=S * 3 * d)  # strides of a Q/K/V/dQ/dK/dV slice inside [M,3d]
-            # dPd = dctx · Vᵀ
-            self._gemm_op(plan, A=dctx, B=(qkv[i], 2 * d), C=dP, lda=d, ldb=3 * d, ldc=S, a_bs0=dh, a_bs1=S * d,
-                          b_bs0=q_s["bs0"], b_bs1=q_s["bs1"], c_bs0=S * S, c_bs1=H * S * S, M=S, N=S, K=dh, **hb)
-            # dV = Pdᵀ · dctx
-            self._gemm_op(plan, A=Pd[i], B=dctx, C=(dqkv, 2 * d), lda=S, ldb=d, ldc=3 * d, a_bs0=S * S, a_bs1=H * S * S,
-                          b_bs0=dh, b_bs1=S * d, c_bs0=q_s["bs0"], c_bs1=q_s["bs1"], M=S, N=dh, K=S, a_t=True, b_t=True,
-                          **hb)
-            op(lambda i=i: K.softmax_bwd(P[i], dP, p_drop=p_att, site=i * 8 + 1, state=st))
-            # dQ = scale * dS · K
-            self._gemm_op(plan, A=dP, B=(qkv[i], d), C=dqkv, lda=S, ldb=3 * d, ldc=3 * d, a_bs0=S * S, a_bs1=H * S * S,
-                          b_bs0=q_s["bs0"], b_bs1=q_s["bs1"], c_bs0=q_s["bs0"], c_bs1=q_s["bs1"], M=S, N=dh, K=S,
-                          b_t=True, alpha=scale, **hb)
-            # dK = scale * dSᵀ · Q
-            self._gemm_op(plan, A=dP, B=qkv[i], C=(dqkv, d), lda=S, ldb=3 * d, ldc=3 * d, a_bs0=S * S, a_bs1=H * S * S,
-                          b_bs0=q_s["bs0"], b_bs1=q_s["bs1"], c_bs0=q_s["bs0"], c_bs1=q_s["bs1"], M=S, N=dh, K=S,
-                          a_t=True, b_t=True, alpha=scale, **hb)
+            if fused:
+                op(lambda i=i: K.attn_bwd(qkv[i], ctx[i], dctx, lse[i], mask, dqkv, attn_ws, B, H, S, scale,
+                                          p_drop=p_att, site=i * 8 + 1, state=st), 3)
+            else:
+                self._attention_bwd_unfused(plan, i, qkv, Pd, P, dP, dctx, dqkv, B, S, H, dh, d, scale, p_att, st, op)
             # QKV projection: dWqkv, dbqkv, dx = dqkv·Wqkv + d(r1)
             self._linear_bwd(plan, dqkv, x_in[i], pfx + "qkv", dx, M, epilogue=G.EPI_ADD, aux=bufA, ldaux=d)
             self.dp.after_grads(plan, [pfx + n for n in ("ln1.weight", "ln1.bias", "out.weight", "out.bias",

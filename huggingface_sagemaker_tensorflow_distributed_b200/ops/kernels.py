@@ -68,13 +68,17 @@ def _register(lib) -> None:
     lib.hstd_colsum_partials_floats.restype = i64
     lib.hstd_softmax_fwd.argtypes = [vp, vp, vp, i32, i32, i32, i32, f32, u32, vp, vp]
     lib.hstd_softmax_bwd.argtypes = [vp, vp, i32, i32, i32, i32, f32, u32, vp, vp]
+    lib.hstd_attn_fwd.argtypes = [vp, vp, vp, vp, i32, i32, i32, f32, f32, u32, vp, vp]
+    lib.hstd_attn_bwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, f32, f32, u32, vp, vp]
+    lib.hstd_attn_bwd_workspace_bytes.argtypes = [i32, i32, i32]
+    lib.hstd_attn_bwd_workspace_bytes.restype = i64
     lib.hstd_position_ids.argtypes = [vp, vp, i32, i32, i32, i32, vp]
     lib.hstd_embed_bwd.argtypes = [vp, vp, vp, vp, vp, i32, i32, vp]
     lib.hstd_head_fwd.argtypes = [C.POINTER(HeadArgs), vp]
     lib.hstd_head_bwd.argtypes = [C.POINTER(HeadArgs), vp]
     for n in ("hstd_step_state_init", "hstd_step_prologue", "hstd_metrics_reset", "hstd_adamw_flat", "hstd_ln_fwd",
               "hstd_ln_bwd", "hstd_colsum", "hstd_softmax_fwd", "hstd_softmax_bwd", "hstd_position_ids",
-              "hstd_embed_bwd", "hstd_head_fwd", "hstd_head_bwd"):
+              "hstd_embed_bwd", "hstd_head_fwd", "hstd_head_bwd", "hstd_attn_fwd", "hstd_attn_bwd"):
         getattr(lib, n).restype = C.c_int
 
 
@@ -161,6 +165,23 @@ def softmax_bwd(p, dpd, p_drop=0.0, site=0, state=None, stream=None):
     B, H, Sq, Sk = p.shape
     _lib.check(_lib.load().hstd_softmax_bwd(p.data_ptr(), dpd.data_ptr(), B, H, Sq, Sk, p_drop, site, _p(state),
                                             _s(stream)), "softmax_bwd")
+
+
+# ----------------------------------------------------------------------------- fused attention
+def attn_fwd(qkv, ctx, lse, key_mask, B, H, S, scale, p_drop=0.0, site=0, state=None, stream=None):
+    _lib.check(_lib.load().hstd_attn_fwd(qkv.data_ptr(), ctx.data_ptr(), _p(lse), key_mask.data_ptr(), B, H, S, scale,
+                                         p_drop, site, _p(state), _s(stream)), "attn_fwd")
+
+
+def attn_bwd_workspace_bytes(B, H, S) -> int:
+    return _lib.load().hstd_attn_bwd_workspace_bytes(B, H, S)
+
+
+def attn_bwd(qkv, ctx, dctx, lse, key_mask, dqkv, workspace, B, H, S, scale, p_drop=0.0, site=0, state=None,
+             stream=None):
+    _lib.check(_lib.load().hstd_attn_bwd(qkv.data_ptr(), ctx.data_ptr(), dctx.data_ptr(), lse.data_ptr(),
+                                         key_mask.data_ptr(), dqkv.data_ptr(), workspace.data_ptr(), B, H, S, scale,
+                                         p_drop, site, _p(state), _s(stream)), "attn_bwd")
 
 
 # ----------------------------------------------------------------------------- embeddings

@@ -181,6 +181,21 @@ int hstd_softmax_fwd(void* scores_p, void* pd, const int32_t* key_mask, int B, i
 int hstd_softmax_bwd(const void* p, void* dpd_ds, int B, int H, int Sq, int Sk, float p_drop, uint32_t site,
                      const hstd_step_state* st, void* stream);
 
+/* ------------------------------------------------------------------ fused attention (K3)
+ * Flash-style attention on tcgen05: ctx = dropout(softmax(Q Kᵀ * scale + key mask)) V per
+ * (batch, head), reading Q/K/V in place from the fused projection output qkv [B*S, 3*H*64]
+ * (Q | K | V column blocks) and writing ctx [B*S, H*64].  head_dim is 64, S in {128..512}.
+ * The [B,H,S,S] probabilities never touch memory; forward saves only lse [B,H,S] (fp32).
+ * Backward consumes qkv, ctx, dctx and lse and writes dqkv [B*S, 3*H*64];
+ * `workspace` = hstd_attn_bwd_workspace_bytes(B,H,S) bytes of caller scratch.
+ * Dropout uses the same Philox stream as hstd_softmax_fwd (same site/seed/step => same mask). */
+int hstd_attn_fwd(const void* qkv, void* ctx, float* lse, const int32_t* key_mask, int B, int H, int S, float scale,
+                  float p_drop, uint32_t site, const hstd_step_state* st, void* stream);
+int hstd_attn_bwd(const void* qkv, const void* ctx, const void* dctx, const float* lse, const int32_t* key_mask,
+                  void* dqkv, void* workspace, int B, int H, int S, float scale, float p_drop, uint32_t site,
+                  const hstd_step_state* st, void* stream);
+int64_t hstd_attn_bwd_workspace_bytes(int B, int H, int S);
+
 /* ------------------------------------------------------------------ embeddings (K1)
  * position ids: mode 0 = arange(S); mode 1 = RoBERTa (cumsum(ids != pad) * (ids != pad) + pad). */
 int hstd_position_ids(const int32_t* ids, int32_t* pos_ids, int B, int S, int mode, int pad_id, void* stream);

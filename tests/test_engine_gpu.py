@@ -21,13 +21,14 @@ def _batch(cfg, B, S, seed=0):
     return next(iter(BatchedDataset(ds, B)))
 
 
-@pytest.mark.parametrize("name", ["tiny-distilbert-gpu", "tiny-bert-gpu", "tiny-roberta-gpu"])
-def test_one_step_matches_autograd_oracle(name):
+@pytest.mark.parametrize("name,fused", [("tiny-distilbert-gpu", True), ("tiny-bert-gpu", True),
+                                        ("tiny-roberta-gpu", True), ("tiny-bert-gpu", False)])
+def test_one_step_matches_autograd_oracle(name, fused):
     from huggingface_sagemaker_tensorflow_distributed_b200.models.reference import EncoderForSequenceClassification
     from huggingface_sagemaker_tensorflow_distributed_b200.optim import Adam
-    model = _mk(name, dropout=0.0, use_cuda_graph=False)
+    model = _mk(name, dropout=0.0, use_cuda_graph=False, fused_attention=fused)
     eng, cfg = model.backend, model.cfg
-    B, S = 4, 128
+    B, S = 4, 256
     feats, labels = _batch(cfg, B, S)
     model.compile(optimizer=Adam(learning_rate=0.0))
     eng.setup_training(model.optimizer, 10, B, S)
@@ -49,7 +50,7 @@ def test_one_step_matches_autograd_oracle(name):
     for n, p in ref.named_parameters():
         g, gr = eng.Gr(n).float(), p.grad
         rel = (g - gr).norm() / (gr.norm() + 1e-12)
-        if not (rel < 0.06 or (g - gr).abs().max() < 2e-4):
+        if not (rel < 0.09 or (g - gr).abs().max() < 2e-4):
             bad.append((n, rel.item(), gr.norm().item()))
     assert not bad, bad
 
