@@ -4,9 +4,10 @@
 // The [B,H,S,S] probability tensor is never written to memory (the reference's TF graph
 // materialises it twice: model.fit at scripts/train.py:145).
 //
-// head_dim = 64, S ∈ {128, 256, 384, 512}.  One CTA = 5 warps: warps 0-3 are the softmax /
-// epilogue warps (thread t owns TMEM lane t = one query row), one lane of warp 4 issues
-// every TMA and tcgen05.mma.
+// head_dim = 64, S ∈ {128, 256, 384, 512}.  One CTA = 9 warps: warps 0-7 are the softmax /
+// epilogue warps (two threads per TMEM lane = query row, each owning half of the columns),
+// one lane of warp 8 issues every TMA and tcgen05.mma.  Key chunks that are entirely padding
+// are skipped (they contribute exactly zero).
 //
 //  forward  (CTA = 128 query rows of one (batch, head)):
 //     S_c = Q·K_cᵀ for all key chunks c (TMEM 128 columns each) → exact row max over all
@@ -26,7 +27,9 @@
 
 namespace hstd {
 
-constexpr int AT_THREADS = 160;
+constexpr int AT_SOFTMAX_WARPS = 8;               // two threads per query row (column halves)
+constexpr int AT_THREADS = (AT_SOFTMAX_WARPS + 1) * 32;
+constexpr int AT_ST = AT_SOFTMAX_WARPS * 32;      // softmax / epilogue threads
 constexpr int TILE = 128;        // query rows / keys per tile
 constexpr int DH = 64;           // head dim
 constexpr uint32_t TILE_BYTES = TILE * DH * 2;   // 16 KiB: [128 rows x 128 B]
@@ -52,9 +55,10 @@ __device__ __forceinline__ uint32_t swz(uint32_t row, uint32_t chunk) { return r
 
 __device__ __forceinline__ float fast_exp2(float x) {
   float y;
-  asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+__device__ __forceinline__ void softmax_warps_sync() { asm volatile("bar.sync 1, %0;" ::"n"(AT_ST) : "memory"); }
 
 // Writes 32 consecutive columns [col0, col0+32) of row `row` (bf16) into a K-major SW128
 // tile made of 64-column atoms of 16 KiB each.
@@ -68,6 +72,30 @@ __device__ __forceinline__ void store_row32(uint8_t* tile, uint32_t row, uint32_
     *reinterpret_cast<uint4*>(atom + swz(row, chunk0 + c)) = o;
   }
 }
+__device__ __forceinline__ void store_row32_zero(uint8_t* tile, uint32_t row, uint32_t col0) {
+  uint8_t* atom = tile + (col0 >> 6) * TILE_BYTES;
+  const uint32_t chunk0 = (col0 & 63u) >> 3;
+#pragma unroll
+  for (int c = 0; c < 4; ++c) *reinterpret_cast<uint4*>(atom + swz(row, chunk0 + c)) = make_uint4(0, 0, 0, 0);
+}
+// 32 fp32 TMEM values scaled and stored as 32 bf16 (64 contiguous bytes)
+__device__ __forceinline__ void store_out32(__nv_bfloat16* out, const uint32_t (&v)[32], float sc) {
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    uint4 o = make_uint4(pack_bf16x2(__uint_as_float(v[8 * c]) * sc, __uint_as_float(v[8 * c + 1]) * sc),
+                         pack_bf16x2(__uint_as_float(v[8 * c + 2]) * sc, __uint_as_float(v[8 * c + 3]) * sc),
+                         pack_bf16x2(__uint_as_float(v[8 * c + 4]) * sc, __uint_as_float(v[8 * c + 5]) * sc),
+                         pack_bf16x2(__uint_as_float(v[8 * c + 6]) * sc, __uint_as_float(v[8 * c + 7]) * sc));
+    *reinterpret_cast<uint4*>(out + c * 8) = o;
+  }
+}
+// Ballot the validity of `nwords*32` keys starting at key0 into smem words (warps 0..7).
+__device__ __forceinline__ void build_mask_bits(uint32_t* bits, const int32_t* key_mask, int nwords, int warp, int lane) {
+  for (int w = warp; w < nwords; w += AT_SOFTMAX_WARPS) {
+    const uint32_t b = __ballot_sync(0xffffffffu, key_mask[w * 32 + lane] != 0);
+    if (lane == 0) bits[w] = b;
+  }
+}
 
 // ============================================================================ forward
 template <int NC>
@@ -78,13 +106,14 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
   constexpr uint32_t IDESC_S = make_idesc_bf16(TILE, TILE, false, false);
   constexpr uint32_t IDESC_O = make_idesc_bf16(TILE, DH, false, true);
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* sQ = smem;
   uint8_t* sK = sQ + TILE_BYTES;
   uint8_t* sV = sK + NC * TILE_BYTES;
   uint8_t* sP = sV + NC * TILE_BYTES;  // 2 buffers
-  float* sBias = reinterpret_cast<float*>(sP + 2 * P_BYTES);  // [NC*128]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sBias + NC * TILE);
+  float* sRed = reinterpret_cast<float*>(sP + 2 * P_BYTES);  // [2][128] exchange between column halves
+  uint32_t* sBits = reinterpret_cast<uint32_t*>(sRed + 2 * TILE);  // [NC*4] key validity, 32 keys per word
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sBits + 16);
   uint64_t* bar_qk = bars;
   uint64_t* bar_v = bars + 1;
   uint64_t* bar_o = bars + 2;
@@ -95,38 +124,42 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
-  const int Sk = NC * TILE;
 
-  if (warp == 4) {
+  if (warp == AT_SOFTMAX_WARPS) {
     if (lane == 0) {
       tma_prefetch_desc(&tm_q); tma_prefetch_desc(&tm_k); tma_prefetch_desc(&tm_v);
       mbar_init(bar_qk, 1); mbar_init(bar_v, 1); mbar_init(bar_o, 1);
       for (int c = 0; c < NC; ++c) mbar_init(&bar_s[c], 1);
-      for (int i = 0; i < 2; ++i) { mbar_init(&bar_p[i], 128); mbar_init(&bar_pfree[i], 1); }
+      for (int i = 0; i < 2; ++i) { mbar_init(&bar_p[i], AT_ST); mbar_init(&bar_pfree[i], 1); }
       fence_mbar_init();
     }
     __syncwarp();
     tmem_alloc(tmem_slot, TMEM_COLS);
     tmem_relinquish();
   } else {
-    for (int i = threadIdx.x; i < Sk; i += 128) sBias[i] = p.key_mask[int64_t(b) * p.S + i] ? 0.f : -INFINITY;
+    build_mask_bits(sBits, p.key_mask + int64_t(b) * p.S, NC * 4, warp, lane);
   }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  // key chunks after the last valid key contribute exactly zero: skip them everywhere
+  int nc = 1;
+#pragma unroll
+  for (int w = 0; w < NC * 4; ++w)
+    if (sBits[w] != 0) nc = (w >> 2) + 1;
 
-  if (warp == 4) {
+  if (warp == AT_SOFTMAX_WARPS) {
     if (lane == 0) {
-      mbar_expect_tx(bar_qk, (1 + NC) * TILE_BYTES);
+      mbar_expect_tx(bar_qk, (1 + nc) * TILE_BYTES);
       tma_load_4d(sQ, &tm_q, bar_qk, 0, qt * TILE, h, b);
-      for (int c = 0; c < NC; ++c) tma_load_4d(sK + c * TILE_BYTES, &tm_k, bar_qk, 0, c * TILE, h, b);
-      mbar_expect_tx(bar_v, NC * TILE_BYTES);
-      for (int c = 0; c < NC; ++c) tma_load_4d(sV + c * TILE_BYTES, &tm_v, bar_v, 0, c * TILE, h, b);
+      for (int c = 0; c < nc; ++c) tma_load_4d(sK + c * TILE_BYTES, &tm_k, bar_qk, 0, c * TILE, h, b);
+      mbar_expect_tx(bar_v, nc * TILE_BYTES);
+      for (int c = 0; c < nc; ++c) tma_load_4d(sV + c * TILE_BYTES, &tm_v, bar_v, 0, c * TILE, h, b);
       mbar_wait(bar_qk, 0);
       tc_fence_after();
       const uint32_t q_addr = smem_u32(sQ);
-      for (int c = 0; c < NC; ++c) {
+      for (int c = 0; c < nc; ++c) {
         const uint32_t k_addr = smem_u32(sK + c * TILE_BYTES);
 #pragma unroll
         for (int k = 0; k < DH / 16; ++k)
@@ -135,7 +168,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
         umma_commit(&bar_s[c]);
       }
       mbar_wait(bar_v, 0);
-      for (int c = 0; c < NC; ++c) {
+      for (int c = 0; c < nc; ++c) {
         const int buf = c & 1;
         mbar_wait(&bar_p[buf], (c >> 1) & 1);
         tc_fence_after();
@@ -150,52 +183,70 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
       umma_commit(bar_o);
     }
   } else {
-    const uint32_t row = threadIdx.x;                       // 0..127 = TMEM lane
-    const uint32_t t_row = tmem + ((uint32_t(warp) * 32u) << 16);
+    const int quarter = warp & 3, half = warp >> 2;
+    const uint32_t row = quarter * 32 + lane;               // TMEM lane = query row of the tile
+    const uint32_t t_row = tmem + ((uint32_t(quarter) * 32u) << 16);
     const float scale2 = p.scale * LOG2E;
-    // ---- pass 1: exact row maximum over every key
+    // ---- pass 1: exact row maximum over every valid key (this thread: its column half)
     float mx = -INFINITY;
-    for (int c = 0; c < NC; ++c) {
+    for (int c = 0; c < nc; ++c) {
       mbar_wait(&bar_s[c], 0);
       tc_fence_after();
 #pragma unroll 1
-      for (int sb = 0; sb < 4; ++sb) {
+      for (int sbi = 0; sbi < 2; ++sbi) {
+        const int sb = half * 2 + sbi;
+        const uint32_t bits = sBits[c * 4 + sb];
+        if (bits == 0) continue;  // warp-uniform
         uint32_t v[32];
         tmem_ld_32x32(t_row + c * TILE + sb * 32, v);
         tmem_ld_wait();
+        if (bits == 0xffffffffu) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(v[j]) + sBias[c * TILE + sb * 32 + j]);
+          for (int j = 0; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(v[j]));
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) mx = fmaxf(mx, ((bits >> j) & 1u) ? __uint_as_float(v[j]) : -INFINITY);
+        }
       }
     }
+    sRed[half * TILE + row] = mx;
+    softmax_warps_sync();
+    mx = fmaxf(mx, sRed[(half ^ 1) * TILE + row]);
     const float m2 = (mx == -INFINITY) ? 0.f : mx * scale2;
     // ---- pass 2: probabilities -> smem (bf16), running row sum
     const Dropout dr = make_dropout(p.st, p.p_drop, p.site);
     const uint64_t row_base = (uint64_t(b) * p.H + h) * p.S + uint64_t(qt) * TILE + row;  // global score row
     float l = 0.f;
-    for (int c = 0; c < NC; ++c) {
+    for (int c = 0; c < nc; ++c) {
       const int buf = c & 1;
       if (c >= 2) mbar_wait(&bar_pfree[buf], ((c - 2) >> 1) & 1);
       uint8_t* pt = sP + buf * P_BYTES;
 #pragma unroll 1
-      for (int sb = 0; sb < 4; ++sb) {
+      for (int sbi = 0; sbi < 2; ++sbi) {
+        const int sb = half * 2 + sbi;
+        const uint32_t bits = sBits[c * 4 + sb];
+        if (bits == 0) {
+          store_row32_zero(pt, row, sb * 32);
+          continue;
+        }
         uint32_t v[32];
         tmem_ld_32x32(t_row + c * TILE + sb * 32, v);
         tmem_ld_wait();
         float f[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
-          const float s = __uint_as_float(v[j]) + sBias[c * TILE + sb * 32 + j];
-          f[j] = fast_exp2(s * scale2 - m2);
+          f[j] = fast_exp2(__uint_as_float(v[j]) * scale2 - m2);
+          if (bits != 0xffffffffu) f[j] = ((bits >> j) & 1u) ? f[j] : 0.f;
           l += f[j];
         }
         if (dr.active()) {
-          const uint64_t e0 = row_base * Sk + c * TILE + sb * 32;
+          const uint64_t e0 = row_base * p.S + c * TILE + sb * 32;
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            float m[8];
-            dropout_mask8(dr, (e0 >> 3) + g, m);
+          for (int g = 0; g < 2; ++g) {
+            float m[16];
+            dropout_mask16(dr, (e0 >> 4) + g, m);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) f[8 * g + j] *= m[j];
+            for (int j = 0; j < 16; ++j) f[16 * g + j] *= m[j];
           }
         }
         store_row32(pt, row, sb * 32, f);
@@ -204,30 +255,26 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
       fence_proxy_async_smem();
       mbar_arrive(&bar_p[buf]);
     }
-    // ---- epilogue: O / l -> ctx, log-sum-exp
+    softmax_warps_sync();  // everyone has read the partner maxima: sRed can be reused
+    sRed[half * TILE + row] = l;
+    softmax_warps_sync();
+    l += sRed[(half ^ 1) * TILE + row];
+    // ---- epilogue: O / l -> ctx (this thread: 32 of the 64 output columns), log-sum-exp
     mbar_wait(bar_o, 0);
     tc_fence_after();
     const float inv_l = l > 0.f ? 1.f / l : 0.f;
-    __nv_bfloat16* out = p.ctx + (int64_t(b) * p.S + qt * TILE + row) * (int64_t(p.H) * DH) + h * DH;
-#pragma unroll
-    for (int half = 0; half < 2; ++half) {
+    __nv_bfloat16* out = p.ctx + (int64_t(b) * p.S + qt * TILE + row) * (int64_t(p.H) * DH) + h * DH + half * 32;
+    {
       uint32_t v[32];
       tmem_ld_32x32(t_row + half * 32, v);
       tmem_ld_wait();
-#pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        uint4 o = make_uint4(pack_bf16x2(__uint_as_float(v[8 * c]) * inv_l, __uint_as_float(v[8 * c + 1]) * inv_l),
-                             pack_bf16x2(__uint_as_float(v[8 * c + 2]) * inv_l, __uint_as_float(v[8 * c + 3]) * inv_l),
-                             pack_bf16x2(__uint_as_float(v[8 * c + 4]) * inv_l, __uint_as_float(v[8 * c + 5]) * inv_l),
-                             pack_bf16x2(__uint_as_float(v[8 * c + 6]) * inv_l, __uint_as_float(v[8 * c + 7]) * inv_l));
-        *reinterpret_cast<uint4*>(out + half * 32 + c * 8) = o;
-      }
+      store_out32(out, v, inv_l);
     }
-    if (p.lse) p.lse[row_base] = (mx == -INFINITY ? 0.f : mx * p.scale) + __logf(fmaxf(l, 1e-30f));
+    if (half == 0 && p.lse) p.lse[row_base] = (mx == -INFINITY ? 0.f : mx * p.scale) + __logf(fmaxf(l, 1e-30f));
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 4) {
+  if (warp == AT_SOFTMAX_WARPS) {
     tc_fence_after();
     tmem_dealloc(tmem, TMEM_COLS);
   }
@@ -267,15 +314,15 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
   constexpr uint32_t IDESC_T = make_idesc_bf16(TILE, DH, true, true);       // Pdᵀ·dO, dSᵀ·Q
   constexpr uint32_t IDESC_Q = make_idesc_bf16(TILE, DH, false, true);      // dS·K
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* sK = smem;
   uint8_t* sV = sK + TILE_BYTES;
   uint8_t* sQ = sV + TILE_BYTES;        // 2 buffers
   uint8_t* sDO = sQ + 2 * TILE_BYTES;   // 2 buffers
   uint8_t* sPd = sDO + 2 * TILE_BYTES;  // 32 KiB
   uint8_t* sDS = sPd + P_BYTES;         // 32 KiB
-  float* sBias = reinterpret_cast<float*>(sDS + P_BYTES);  // [128]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sBias + TILE);
+  uint32_t* sBits = reinterpret_cast<uint32_t*>(sDS + P_BYTES);  // [4]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sBits + 4);
   uint64_t* bar_kv = bars;
   uint64_t* bar_q = bars + 1;       // [2]
   uint64_t* bar_sdp = bars + 3;
@@ -287,26 +334,42 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int kt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
   const int S = p.S;
+  const int d = p.H * DH;
 
-  if (warp == 4) {
+  if (warp < AT_SOFTMAX_WARPS) build_mask_bits(sBits, p.key_mask + int64_t(b) * S + kt * TILE, 4, warp, lane);
+  __syncthreads();
+  if ((sBits[0] | sBits[1] | sBits[2] | sBits[3]) == 0) {
+    // every key of this tile is padding: its dK, dV and its dQ contributions are exactly zero
+    const uint4 z = make_uint4(0, 0, 0, 0);
+    for (int i = threadIdx.x; i < TILE * 8 * 2; i += AT_THREADS) {  // dK, dV: 128 rows x 128 B each
+      const int which = i / (TILE * 8), r = (i / 8) % TILE, c = i % 8;
+      *reinterpret_cast<uint4*>(p.dqkv + (int64_t(b) * S + kt * TILE + r) * (3 * int64_t(d)) + (which + 1) * int64_t(d) +
+                                h * DH + c * 8) = z;
+    }
+    for (int i = threadIdx.x; i < S * 8; i += AT_THREADS) {
+      const int r = i / 8, c = i % 8;
+      *reinterpret_cast<uint4*>(p.dq_part + (int64_t(kt) * p.B * S + int64_t(b) * S + r) * d + h * DH + c * 8) = z;
+    }
+    return;
+  }
+
+  if (warp == AT_SOFTMAX_WARPS) {
     if (lane == 0) {
       tma_prefetch_desc(&tm_q); tma_prefetch_desc(&tm_k); tma_prefetch_desc(&tm_v); tma_prefetch_desc(&tm_do);
       mbar_init(bar_kv, 1); mbar_init(&bar_q[0], 1); mbar_init(&bar_q[1], 1);
-      mbar_init(bar_sdp, 1); mbar_init(bar_pds, 128); mbar_init(bar_dq, 1); mbar_init(bar_dqread, 128);
+      mbar_init(bar_sdp, 1); mbar_init(bar_pds, AT_ST); mbar_init(bar_dq, 1); mbar_init(bar_dqread, AT_ST);
       fence_mbar_init();
     }
     __syncwarp();
     tmem_alloc(tmem_slot, TMEM_COLS);
     tmem_relinquish();
-  } else {
-    sBias[threadIdx.x] = p.key_mask[int64_t(b) * S + kt * TILE + threadIdx.x] ? 0.f : -INFINITY;
   }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
 
-  if (warp == 4) {
+  if (warp == AT_SOFTMAX_WARPS) {
     if (lane == 0) {
       mbar_expect_tx(bar_kv, 2 * TILE_BYTES);
       tma_load_4d(sK, &tm_k, bar_kv, 0, kt * TILE, h, b);
@@ -363,11 +426,11 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
       }
     }
   } else {
-    const uint32_t row = threadIdx.x;
-    const uint32_t t_row = tmem + ((uint32_t(warp) * 32u) << 16);
+    const int quarter = warp & 3, half = warp >> 2;
+    const uint32_t row = quarter * 32 + lane;
+    const uint32_t t_row = tmem + ((uint32_t(quarter) * 32u) << 16);
     const float scale2 = p.scale * LOG2E;
     const Dropout dr = make_dropout(p.st, p.p_drop, p.site);
-    const int d = p.H * DH;
     for (int i = 0; i < NQ; ++i) {
       const uint64_t srow = (uint64_t(b) * p.H + h) * S + uint64_t(i) * TILE + row;  // global score row
       const float lse2 = p.lse[srow] * LOG2E;
@@ -375,7 +438,14 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
       mbar_wait(bar_sdp, i & 1);
       tc_fence_after();
 #pragma unroll 1
-      for (int sb = 0; sb < 4; ++sb) {
+      for (int sbi = 0; sbi < 2; ++sbi) {
+        const int sb = half * 2 + sbi;
+        const uint32_t bits = sBits[sb];
+        if (bits == 0) {
+          store_row32_zero(sPd, row, sb * 32);
+          store_row32_zero(sDS, row, sb * 32);
+          continue;
+        }
         uint32_t vs[32], vd[32];
         tmem_ld_32x32(t_row + C_S + sb * 32, vs);
         tmem_ld_32x32(t_row + C_DP + sb * 32, vd);
@@ -383,21 +453,22 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
         float pd[32], ds[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
-          const float s = __uint_as_float(vs[j]) + sBias[sb * 32 + j];
-          pd[j] = fast_exp2(s * scale2 - lse2);  // P (masked keys -> 0)
-          ds[j] = __uint_as_float(vd[j]);        // dPd
+          float pj = fast_exp2(__uint_as_float(vs[j]) * scale2 - lse2);  // P
+          if (bits != 0xffffffffu) pj = ((bits >> j) & 1u) ? pj : 0.f;
+          pd[j] = pj;
+          ds[j] = __uint_as_float(vd[j]);  // dPd
         }
         if (dr.active()) {
           const uint64_t e0 = srow * S + kt * TILE + sb * 32;
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            float m[8];
-            dropout_mask8(dr, (e0 >> 3) + g, m);
+          for (int g = 0; g < 2; ++g) {
+            float m[16];
+            dropout_mask16(dr, (e0 >> 4) + g, m);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const float pj = pd[8 * g + j];
-              ds[8 * g + j] = pj * (ds[8 * g + j] * m[j] - dl);
-              pd[8 * g + j] = pj * m[j];
+            for (int j = 0; j < 16; ++j) {
+              const float pj = pd[16 * g + j];
+              ds[16 * g + j] = pj * (ds[16 * g + j] * m[j] - dl);
+              pd[16 * g + j] = pj * m[j];
             }
           }
         } else {
@@ -410,53 +481,34 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
       tc_fence_before();
       fence_proxy_async_smem();
       mbar_arrive(bar_pds);
-      // dQ partial of this (query tile, key tile)
+      // dQ partial of this (query tile, key tile): this thread stores 32 of the 64 columns
       mbar_wait(bar_dq, i & 1);
       tc_fence_after();
-      __nv_bfloat16* out = p.dq_part + (int64_t(kt) * p.B * S + int64_t(b) * S + i * TILE + row) * d + h * DH;
-#pragma unroll
-      for (int half = 0; half < 2; ++half) {
+      {
         uint32_t v[32];
         tmem_ld_32x32(t_row + C_DQ + half * 32, v);
         tmem_ld_wait();
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          uint4 o = make_uint4(
-              pack_bf16x2(__uint_as_float(v[8 * c]) * p.scale, __uint_as_float(v[8 * c + 1]) * p.scale),
-              pack_bf16x2(__uint_as_float(v[8 * c + 2]) * p.scale, __uint_as_float(v[8 * c + 3]) * p.scale),
-              pack_bf16x2(__uint_as_float(v[8 * c + 4]) * p.scale, __uint_as_float(v[8 * c + 5]) * p.scale),
-              pack_bf16x2(__uint_as_float(v[8 * c + 6]) * p.scale, __uint_as_float(v[8 * c + 7]) * p.scale));
-          *reinterpret_cast<uint4*>(out + half * 32 + c * 8) = o;
-        }
+        store_out32(p.dq_part + (int64_t(kt) * p.B * S + int64_t(b) * S + i * TILE + row) * d + h * DH + half * 32, v,
+                    p.scale);
       }
       tc_fence_before();
       mbar_arrive(bar_dqread);
     }
-    // dK (x scale) and dV of this key tile; the last bar_dq wait above covered all MMAs
-    __nv_bfloat16* orow = p.dqkv + (int64_t(b) * S + kt * TILE + row) * (3 * int64_t(d)) + h * DH;
-#pragma unroll
-    for (int which = 0; which < 2; ++which) {  // 0: dK -> slot 1, 1: dV -> slot 2
-      const float sc = which == 0 ? p.scale : 1.f;
-      __nv_bfloat16* out = orow + (which + 1) * int64_t(d);
-#pragma unroll
-      for (int half = 0; half < 2; ++half) {
-        uint32_t v[32];
-        tmem_ld_32x32(t_row + (which == 0 ? C_DK : C_DV) + half * 32, v);
-        tmem_ld_wait();
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          uint4 o = make_uint4(pack_bf16x2(__uint_as_float(v[8 * c]) * sc, __uint_as_float(v[8 * c + 1]) * sc),
-                               pack_bf16x2(__uint_as_float(v[8 * c + 2]) * sc, __uint_as_float(v[8 * c + 3]) * sc),
-                               pack_bf16x2(__uint_as_float(v[8 * c + 4]) * sc, __uint_as_float(v[8 * c + 5]) * sc),
-                               pack_bf16x2(__uint_as_float(v[8 * c + 6]) * sc, __uint_as_float(v[8 * c + 7]) * sc));
-          *reinterpret_cast<uint4*>(out + half * 32 + c * 8) = o;
-        }
-      }
+    // dK (x scale) and dV of this key tile (TMEM lane = key row); the last bar_dq wait covered all MMAs
+    __nv_bfloat16* orow = p.dqkv + (int64_t(b) * S + kt * TILE + row) * (3 * int64_t(d)) + h * DH + half * 32;
+    {
+      uint32_t v[32];
+      tmem_ld_32x32(t_row + C_DK + half * 32, v);
+      tmem_ld_wait();
+      store_out32(orow + int64_t(d), v, p.scale);
+      tmem_ld_32x32(t_row + C_DV + half * 32, v);
+      tmem_ld_wait();
+      store_out32(orow + 2 * int64_t(d), v, 1.f);
     }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 4) {
+  if (warp == AT_SOFTMAX_WARPS) {
     tc_fence_after();
     tmem_dealloc(tmem, TMEM_COLS);
   }
@@ -483,8 +535,8 @@ __global__ void __launch_bounds__(256) attn_dq_reduce_kernel(const __nv_bfloat16
   }
 }
 
-static size_t fwd_smem(int nc) { return 1024 + size_t(1 + 2 * nc) * TILE_BYTES + 2 * P_BYTES + nc * TILE * 4 + 256; }
-static size_t bwd_smem() { return 1024 + 6 * size_t(TILE_BYTES) + 2 * P_BYTES + TILE * 4 + 256; }
+static size_t fwd_smem(int nc) { return 1024 + size_t(1 + 2 * nc) * TILE_BYTES + 2 * P_BYTES + 2 * TILE * 4 + 64 + 256; }
+static size_t bwd_smem() { return 1024 + 6 * size_t(TILE_BYTES) + 2 * P_BYTES + 16 + 256; }
 
 template <typename Kern>
 static int set_smem(Kern k, size_t bytes) {

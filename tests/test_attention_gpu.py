@@ -74,7 +74,7 @@ def test_fused_attention_dropout_uses_the_same_mask_as_the_softmax_kernel():
     ctx = torch.empty(B * S, d, dtype=torch.bfloat16, device="cuda")
     lse = torch.empty(B, H, S, device="cuda")
     K.attn_fwd(qkv, ctx, lse, mask, B, H, S, 0.125, p_drop=p, site=5, state=st)
-    p_eff = 1 - 1 / (65536.0 / (65536 - round(p * 65536)))
+    p_eff = round(p * 256) / 256.0
     rctx, _, rgrad = _ref(qkv, mask, B, S, H, dO, drop_keep=keep, p=p_eff)
     _close(ctx, rctx)
     dqkv = torch.empty(B * S, 3 * d, dtype=torch.bfloat16, device="cuda")
