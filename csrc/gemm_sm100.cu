@@ -44,24 +44,34 @@ struct GemmKernelParams {
   float alpha;
 };
 
-template <int BN>
+// Per-CTA smem: with MC == 2 (cta_group::2) each CTA of the pair stages only half of the B tile.
+template <int BN, int MC>
 struct GemmCfg {
-  static constexpr int STAGES = BN == 256 ? 4 : (BN == 128 ? 6 : 8);
-  static constexpr size_t SMEM = 1024 /*align slack*/ + size_t(STAGES) * (BLOCK_M * BLOCK_K * 2 + BN * BLOCK_K * 2) + 256;
+  static constexpr uint32_t A_BYTES = BLOCK_M * BLOCK_K * 2;
+  static constexpr uint32_t B_BYTES = (BN / MC) * BLOCK_K * 2;
+  static constexpr int STAGES = (200 * 1024) / int(A_BYTES + B_BYTES) > 8 ? 8 : (200 * 1024) / int(A_BYTES + B_BYTES);
+  static constexpr size_t SMEM = 1024 /*align slack*/ + size_t(STAGES) * (A_BYTES + B_BYTES) + 256;
 };
 
-template <int BN, bool A_MN, bool B_MN>
+// MC = CTAs per tile along M.  MC == 2 is the 2-SM form (cta_group::2): a cluster of two CTAs
+// computes one 256 x BN tile with a single tcgen05.mma issued by the leader; each CTA stages its
+// own 128 rows of A and half of the B tile, so the per-SM shared-memory traffic (TMA writes +
+// tensor-core reads) drops from 192 to ~125 B/cycle — below the 128 B/cycle port limit that
+// caps the 1-SM form at ~60 % of the tensor peak.
+template <int BN, bool A_MN, bool B_MN, int MC>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                  const GemmKernelParams p) {
-  constexpr int STAGES = GemmCfg<BN>::STAGES;
-  constexpr uint32_t A_BYTES = BLOCK_M * BLOCK_K * 2;
-  constexpr uint32_t B_BYTES = BN * BLOCK_K * 2;
+  constexpr int STAGES = GemmCfg<BN, MC>::STAGES;
+  constexpr uint32_t A_BYTES = GemmCfg<BN, MC>::A_BYTES;
+  constexpr uint32_t B_BYTES = GemmCfg<BN, MC>::B_BYTES;   // per CTA
+  constexpr int BN_LOCAL = BN / MC;                        // B rows staged by this CTA
   constexpr uint32_t TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;
-  constexpr uint32_t IDESC = make_idesc_bf16(BLOCK_M, BN, A_MN, B_MN);
+  constexpr uint32_t IDESC = make_idesc_bf16(BLOCK_M * MC, BN, A_MN, B_MN);
+  constexpr uint16_t PAIR_MASK = (1u << MC) - 1;
 
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + STAGES * A_BYTES;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_b + STAGES * B_BYTES);
@@ -72,67 +82,98 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const int cta_rank = MC > 1 ? int(cluster_ctarank()) : 0;
+  const bool leader = cta_rank == 0;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_b);
     for (int s = 0; s < STAGES; ++s) {
-      mbar_init(&full_bar[s], 1);
+      mbar_init(&full_bar[s], 1);   // MC == 2: only the leader's copy is used
       mbar_init(&empty_bar[s], 1);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tmem_full[i], 1);
-      mbar_init(&tmem_empty[i], NUM_EPI_WARPS);
+      mbar_init(&tmem_empty[i], NUM_EPI_WARPS * MC);  // MC == 2: the leader's copy collects both CTAs' epilogues
     }
     fence_mbar_init();
   }
   if (warp == 1) {
-    tmem_alloc(tmem_slot, TMEM_COLS);
-    tmem_relinquish();
+    if constexpr (MC == 1) {
+      tmem_alloc(tmem_slot, TMEM_COLS);
+      tmem_relinquish();
+    } else {
+      tmem_alloc_2sm(tmem_slot, TMEM_COLS);
+      tmem_relinquish_2sm();
+    }
   }
   tc_fence_before();
   __syncthreads();
+  if constexpr (MC > 1) cluster_sync_all();  // peer barriers are initialised before anything remote lands
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  const int tiles_per_batch = p.tiles_m * p.tiles_n * p.num_splits;
+  const int tiles_mp = (p.tiles_m + MC - 1) / MC;  // M tiles are handed out in groups of MC
+  const int tiles_per_batch = tiles_mp * p.tiles_n * p.num_splits;
   const int total_tiles = tiles_per_batch * p.nb0 * p.nb1;
   const int num_kb_total = (p.K + BLOCK_K - 1) / BLOCK_K;
+  const int first_tile = blockIdx.x / MC, tile_stride = gridDim.x / MC;
 
   if (warp == 0) {
-    // ------------------------------------------------------------ TMA producer
+    // ------------------------------------------------------------ TMA producer (every CTA)
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      for (int tile = first_tile; tile < total_tiles; tile += tile_stride) {
         const int z = tile / tiles_per_batch;
         int r = tile - z * tiles_per_batch;
-        const int split = r / (p.tiles_m * p.tiles_n);
-        r -= split * (p.tiles_m * p.tiles_n);
-        const int tm = r / p.tiles_n, tn = r - tm * p.tiles_n;
+        const int split = r / (tiles_mp * p.tiles_n);
+        r -= split * (tiles_mp * p.tiles_n);
+        const int tmp = r / p.tiles_n, tn = r - tmp * p.tiles_n;
+        const int tm = tmp * MC + cta_rank;  // may be one past the last M tile: TMA zero-fills, nothing is stored
         const int z0 = z % p.nb0, z1 = z / p.nb0;
-        const int m0 = tm * BLOCK_M, n0 = tn * BN;
+        const int m0 = tm * BLOCK_M, n0 = tn * BN + cta_rank * BN_LOCAL;
         const int kb_begin = split * p.kb_per_split;
         const int kb_end = min(num_kb_total, kb_begin + p.kb_per_split);
         for (int kb = kb_begin; kb < kb_end; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
-          mbar_expect_tx(&full_bar[stage], A_BYTES + B_BYTES);
           uint8_t* sa = smem_a + stage * A_BYTES;
           uint8_t* sb = smem_b + stage * B_BYTES;
           const int k0 = kb * BLOCK_K;
-          if constexpr (!A_MN) {
-            tma_load_4d(sa, &tmap_a, &full_bar[stage], k0, m0, z0, z1);
-          } else {
+          if constexpr (MC == 1) {
+            mbar_expect_tx(&full_bar[stage], A_BYTES + B_BYTES);
+            if constexpr (!A_MN) {
+              tma_load_4d(sa, &tmap_a, &full_bar[stage], k0, m0, z0, z1);
+            } else {
 #pragma unroll
-            for (int j = 0; j < BLOCK_M / 64; ++j)
-              tma_load_4d(sa + j * (64 * BLOCK_K * 2), &tmap_a, &full_bar[stage], m0 + 64 * j, k0, z0, z1);
-          }
-          if constexpr (!B_MN) {
-            tma_load_4d(sb, &tmap_b, &full_bar[stage], k0, n0, z0, z1);
-          } else {
+              for (int j = 0; j < BLOCK_M / 64; ++j)
+                tma_load_4d(sa + j * (64 * BLOCK_K * 2), &tmap_a, &full_bar[stage], m0 + 64 * j, k0, z0, z1);
+            }
+            if constexpr (!B_MN) {
+              tma_load_4d(sb, &tmap_b, &full_bar[stage], k0, n0, z0, z1);
+            } else {
 #pragma unroll
-            for (int j = 0; j < BN / 64; ++j)
-              tma_load_4d(sb + j * (64 * BLOCK_K * 2), &tmap_b, &full_bar[stage], n0 + 64 * j, k0, z0, z1);
+              for (int j = 0; j < BN_LOCAL / 64; ++j)
+                tma_load_4d(sb + j * (64 * BLOCK_K * 2), &tmap_b, &full_bar[stage], n0 + 64 * j, k0, z0, z1);
+            }
+          } else {
+            // both CTAs' bytes complete on the leader's barrier
+            if (leader) mbar_expect_tx(&full_bar[stage], MC * (A_BYTES + B_BYTES));
+            const uint32_t bar = mapa_shared(smem_u32(&full_bar[stage]), 0);
+            if constexpr (!A_MN) {
+              tma_load_4d_2sm(sa, &tmap_a, bar, k0, m0, z0, z1);
+            } else {
+#pragma unroll
+              for (int j = 0; j < BLOCK_M / 64; ++j)
+                tma_load_4d_2sm(sa + j * (64 * BLOCK_K * 2), &tmap_a, bar, m0 + 64 * j, k0, z0, z1);
+            }
+            if constexpr (!B_MN) {
+              tma_load_4d_2sm(sb, &tmap_b, bar, k0, n0, z0, z1);
+            } else {
+#pragma unroll
+              for (int j = 0; j < BN_LOCAL / 64; ++j)
+                tma_load_4d_2sm(sb + j * (64 * BLOCK_K * 2), &tmap_b, bar, n0 + 64 * j, k0, z0, z1);
+            }
           }
           if (++stage == STAGES) {
             stage = 0;
@@ -142,15 +183,15 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       }
     }
   } else if (warp == 1) {
-    // ------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
+    // ------------------------------------------------------------ MMA issuer (leader CTA only)
+    if (lane == 0 && leader) {
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      for (int tile = first_tile; tile < total_tiles; tile += tile_stride) {
         int r = tile % tiles_per_batch;
-        const int split = r / (p.tiles_m * p.tiles_n);
+        const int split = r / (tiles_mp * p.tiles_n);
         const int kb_begin = split * p.kb_per_split;
         const int kb_end = min(num_kb_total, kb_begin + p.kb_per_split);
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
@@ -169,15 +210,20 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                                      : make_smem_desc_sw128(a_addr + k * 32, 16, 1024);
             const uint64_t db = B_MN ? make_smem_desc_sw128(b_addr + k * 2048, 64 * BLOCK_K * 2, 1024)
                                      : make_smem_desc_sw128(b_addr + k * 32, 16, 1024);
-            umma_bf16(d_tmem, da, db, IDESC, (kb > kb_begin || k > 0) ? 1u : 0u);
+            if constexpr (MC == 1) umma_bf16(d_tmem, da, db, IDESC, (kb > kb_begin || k > 0) ? 1u : 0u);
+            else umma_bf16_2sm(d_tmem, da, db, IDESC, (kb > kb_begin || k > 0) ? 1u : 0u);
           }
-          umma_commit(&empty_bar[stage]);  // smem stage free once these MMAs retire
+          // smem stage free once these MMAs retire (in both CTAs of a pair)
+          if constexpr (MC == 1) umma_commit(&empty_bar[stage]);
+          else umma_commit_2sm(&empty_bar[stage], PAIR_MASK);
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
           }
         }
-        umma_commit(&tmem_full[acc]);  // accumulator complete
+        // accumulator complete: wake the epilogue warps (of both CTAs)
+        if constexpr (MC == 1) umma_commit(&tmem_full[acc]);
+        else umma_commit_2sm(&tmem_full[acc], PAIR_MASK);
         if (++acc == 2) {
           acc = 0;
           acc_phase ^= 1;
@@ -192,12 +238,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     constexpr int COLS_PER_WARP = BN / 2;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+    for (int tile = first_tile; tile < total_tiles; tile += tile_stride) {
       const int z = tile / tiles_per_batch;
       int r = tile - z * tiles_per_batch;
-      const int split = r / (p.tiles_m * p.tiles_n);
-      r -= split * (p.tiles_m * p.tiles_n);
-      const int tm = r / p.tiles_n, tn = r - tm * p.tiles_n;
+      const int split = r / (tiles_mp * p.tiles_n);
+      r -= split * (tiles_mp * p.tiles_n);
+      const int tmp = r / p.tiles_n, tn = r - tmp * p.tiles_n;
+      const int tm = tmp * MC + cta_rank;
       const int z0 = z % p.nb0, z1 = z / p.nb0;
       const int row = tm * BLOCK_M + quarter * 32 + lane;
       const int col_base = tn * BN + col_half * COLS_PER_WARP;
@@ -290,10 +337,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           }
         }
       }
-      // All TMEM reads of this accumulator buffer are done (wait::ld above): hand it back.
+      // All TMEM reads of this accumulator buffer are done (wait::ld above): hand it back to
+      // the MMA issuer (which lives in the leader CTA).
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+      if (lane == 0) {
+        if (MC == 1 || leader) mbar_arrive(&tmem_empty[acc]);
+        else mbar_arrive_cluster(mapa_shared(smem_u32(&tmem_empty[acc]), 0));
+      }
       if (++acc == 2) {
         acc = 0;
         acc_phase ^= 1;
@@ -303,9 +354,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 
   tc_fence_before();
   __syncthreads();
+  if constexpr (MC > 1) cluster_sync_all();  // no CTA leaves while its peer may still touch its smem / barriers / TMEM
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, TMEM_COLS);
+    if constexpr (MC == 1) tmem_dealloc(tmem_base, TMEM_COLS);
+    else tmem_dealloc_2sm(tmem_base, TMEM_COLS);
   }
 }
 
@@ -338,25 +391,44 @@ int num_sms() {
   return n;
 }
 
-template <int BN, bool A_MN, bool B_MN>
-static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmKernelParams& p, int max_ctas,
-                       cudaStream_t stream) {
-  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN>;
-  constexpr size_t smem = GemmCfg<BN>::SMEM;
+template <int BN, bool A_MN, bool B_MN, int MC>
+static int launch_gemm_mc(const CUtensorMap& ta, const CUtensorMap& tb, const GemmKernelParams& p, int max_ctas,
+                          cudaStream_t stream) {
+  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, MC>;
+  constexpr size_t smem = GemmCfg<BN, MC>::SMEM;
   static bool configured = false;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
     if (e != cudaSuccess) return set_error(-5, std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e));
     configured = true;
   }
-  const int total = p.tiles_m * p.tiles_n * p.num_splits * p.nb0 * p.nb1;
-  int grid = num_sms();
-  if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
-  if (total < grid) grid = total;
-  kern<<<grid, GEMM_THREADS, smem, stream>>>(ta, tb, p);
-  cudaError_t e = cudaGetLastError();
+  const int tiles_mp = (p.tiles_m + MC - 1) / MC;
+  const int total = tiles_mp * p.tiles_n * p.num_splits * p.nb0 * p.nb1;  // cluster-tiles
+  int clusters = num_sms() / MC;
+  if (max_ctas > 0 && max_ctas / MC < clusters) clusters = max_ctas / MC > 0 ? max_ctas / MC : 1;
+  if (total < clusters) clusters = total;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(clusters * MC);
+  cfg.blockDim = dim3(GEMM_THREADS);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = MC;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb, p);
   if (e != cudaSuccess) return set_error(-6, std::string("gemm launch: ") + cudaGetErrorString(e));
   return 0;
+}
+
+template <int BN, bool A_MN, bool B_MN>
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmKernelParams& p, int max_ctas, int mc,
+                       cudaStream_t stream) {
+  if (mc == 2) return launch_gemm_mc<BN, A_MN, B_MN, 2>(ta, tb, p, max_ctas, stream);
+  return launch_gemm_mc<BN, A_MN, B_MN, 1>(ta, tb, p, max_ctas, stream);
 }
 
 static int pick_block_n(int M, int N, int batches, int splits) {
@@ -382,8 +454,12 @@ static int gemm_impl(const hstd_gemm_args* a, int splits, float* workspace, cuda
   else
     rc = get_tmap(&ta, a->A, a->M, a->K, nb0, nb1, a->lda, a->a_bs0, a->a_bs1, 64);
   if (rc) return rc;
+  // 2-SM MMA (256 x BN tile per CTA pair) whenever there are at least two M tiles; the
+  // 64-wide B tile cannot be split between the pair.
+  int mc = (a->M > BLOCK_M && bn >= 128) ? 2 : 1;
+  if (a->cluster_m == 1) mc = 1;
   if (!a->b_mn_major)
-    rc = get_tmap(&tb, a->B, a->K, a->N, nb0, nb1, a->ldb, a->b_bs0, a->b_bs1, bn);
+    rc = get_tmap(&tb, a->B, a->K, a->N, nb0, nb1, a->ldb, a->b_bs0, a->b_bs1, bn / mc);
   else
     rc = get_tmap(&tb, a->B, a->N, a->K, nb0, nb1, a->ldb, a->b_bs0, a->b_bs1, 64);
   if (rc) return rc;
@@ -408,10 +484,10 @@ static int gemm_impl(const hstd_gemm_args* a, int splits, float* workspace, cuda
 
 #define HSTD_GEMM_CASE(BN_)                                                                         \
   if (bn == BN_) {                                                                                  \
-    if (!a->a_mn_major && !a->b_mn_major) return launch_gemm<BN_, false, false>(ta, tb, p, a->max_ctas, stream); \
-    if (!a->a_mn_major && a->b_mn_major) return launch_gemm<BN_, false, true>(ta, tb, p, a->max_ctas, stream);   \
-    if (a->a_mn_major && !a->b_mn_major) return launch_gemm<BN_, true, false>(ta, tb, p, a->max_ctas, stream);   \
-    return launch_gemm<BN_, true, true>(ta, tb, p, a->max_ctas, stream);                            \
+    if (!a->a_mn_major && !a->b_mn_major) return launch_gemm<BN_, false, false>(ta, tb, p, a->max_ctas, mc, stream); \
+    if (!a->a_mn_major && a->b_mn_major) return launch_gemm<BN_, false, true>(ta, tb, p, a->max_ctas, mc, stream);   \
+    if (a->a_mn_major && !a->b_mn_major) return launch_gemm<BN_, true, false>(ta, tb, p, a->max_ctas, mc, stream);   \
+    return launch_gemm<BN_, true, true>(ta, tb, p, a->max_ctas, mc, stream);                            \
   }
   HSTD_GEMM_CASE(64)
   HSTD_GEMM_CASE(128)

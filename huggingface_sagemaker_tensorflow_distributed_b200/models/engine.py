@@ -222,6 +222,13 @@ class EngineBackend:
         g.epilogue, g.alpha = kw.get("epilogue", G.EPI_NONE), kw.get("alpha", 1.0)
         g.block_n, g.max_ctas = kw.get("block_n", 0), kw.get("max_ctas", 0)
         splits = kw.get("splits", 1)
+        if g.nb0 == 1 and g.nb1 == 1 and not kw.get("block_n"):
+            tuned = G.tuned_config(g.M, g.N, g.K, bool(g.a_mn_major), bool(g.b_mn_major))
+            if tuned is not None:
+                g.block_n, cm, tsplits = tuned
+                g.cluster_m = 1 if cm == 1 else 0
+                if g.a_mn_major and g.b_mn_major and g.epilogue == G.EPI_NONE and g.bias is None:
+                    splits = tsplits
         ws = None
         if splits > 1:
             ws = self._shared("splitk_ws", g.M * g.N * splits, torch.float32)
@@ -242,7 +249,7 @@ class EngineBackend:
         tiles = ((N + 127) // 128) * ((Kd + 127) // 128)
         splits = max(1, min(8, round(148 / tiles), M // 512))
         self._gemm_op(plan, A=dy, B=x, C=self.Gr(w_name + ".weight"), lda=N, ldb=Kd, ldc=Kd, M=N, N=Kd, K=M, a_t=True,
-                      b_t=True, splits=splits, block_n=128 if splits > 1 else 0)
+                      b_t=True, splits=splits)
         if bias_grad:
             part = self._shared("colsum_partials", K.colsum_partials_floats(N))
             db = self.Gr(w_name + ".bias")

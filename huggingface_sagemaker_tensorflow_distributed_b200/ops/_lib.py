@@ -28,7 +28,7 @@ class GemmArgs(C.Structure):
         ("nb0", C.c_int32), ("nb1", C.c_int32),
         ("a_mn_major", C.c_int32), ("b_mn_major", C.c_int32),
         ("epilogue", C.c_int32), ("alpha", C.c_float),
-        ("block_n", C.c_int32), ("max_ctas", C.c_int32),
+        ("block_n", C.c_int32), ("max_ctas", C.c_int32), ("cluster_m", C.c_int32),
     ]
 
 

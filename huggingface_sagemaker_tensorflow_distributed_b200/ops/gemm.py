@@ -21,6 +21,27 @@ from . import _lib
 
 EPI_NONE, EPI_GELU, EPI_ADD, EPI_GELU_BWD = 0, 1, 2, 3
 
+_TUNING = None
+
+
+def tuned_config(M: int, N: int, K: int, a_t: bool, b_t: bool):
+    """(block_n, cluster_m, splits) measured best on B200 by tools/gemm_tune.py for this shape,
+    or None (the kernel's own heuristics apply)."""
+    global _TUNING
+    if _TUNING is None:
+        import json
+        import os
+        path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "gemm_tuning.json")
+        try:
+            with open(path) as f:
+                _TUNING = json.load(f)
+        except (OSError, ValueError):
+            _TUNING = {}
+    e = _TUNING.get(f"{M},{N},{K},{int(a_t)},{int(b_t)}")
+    if e is None:
+        return None
+    return int(e["block_n"]), int(e["cluster_m"]), int(e["splits"])
+
 
 def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
     return None if t is None else t.data_ptr()
@@ -40,7 +61,8 @@ def gemm_raw(args: _lib.GemmArgs, stream=None, splits: int = 1, workspace: Optio
 def gemm(A: torch.Tensor, B: torch.Tensor, *, a_t: bool = False, b_t: bool = False,
          bias: Optional[torch.Tensor] = None, epilogue: int = EPI_NONE, aux: Optional[torch.Tensor] = None,
          alpha: float = 1.0, out: Optional[torch.Tensor] = None, block_n: int = 0, splits: int = 1,
-         workspace: Optional[torch.Tensor] = None, max_ctas: int = 0, stream=None) -> torch.Tensor:
+         workspace: Optional[torch.Tensor] = None, max_ctas: int = 0, cluster_m: int = 0,
+         stream=None) -> torch.Tensor:
     """2-D (or 3-D batched, leading batch dim) bf16 GEMM.  See module docstring."""
     assert A.dtype == torch.bfloat16 and B.dtype == torch.bfloat16 and A.is_cuda and B.is_cuda
     batched = A.dim() == 3
@@ -73,6 +95,6 @@ def gemm(A: torch.Tensor, B: torch.Tensor, *, a_t: bool = False, b_t: bool = Fal
     g.ldaux = aux.stride(-2) if aux is not None else 0
     g.M, g.N, g.K, g.nb0, g.nb1 = M, N, K, nb, 1
     g.a_mn_major, g.b_mn_major = int(a_t), int(b_t)
-    g.epilogue, g.alpha, g.block_n, g.max_ctas = epilogue, alpha, block_n, max_ctas
+    g.epilogue, g.alpha, g.block_n, g.max_ctas, g.cluster_m = epilogue, alpha, block_n, max_ctas, cluster_m
     gemm_raw(g, stream, splits, workspace)
     return out

@@ -62,6 +62,7 @@ typedef struct hstd_gemm_args {
   float alpha;
   int32_t block_n; /* 0 = auto, else 64/128/256 */
   int32_t max_ctas; /* 0 = one persistent CTA per SM */
+  int32_t cluster_m; /* 0 = auto (2-CTA clusters multicasting B when M > 128), 1 = no clusters */
 } hstd_gemm_args;
 
 int hstd_gemm_bf16(const hstd_gemm_args* args, void* stream);

@@ -46,34 +46,36 @@ def run_case(M, N, K, a_t, b_t, bn, nb=0, splits=1):
     return ok
 
 
+def _graph_time(fn, iters):
+    """GPU time per call with host launch overhead removed: `iters` calls captured in one CUDA graph."""
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for _ in range(iters):
+            fn()
+    g.replay()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    g.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters
+
+
 def bench(M, N, K, a_t, b_t, bn, nb=0, iters=20, **kw):
     sh = (nb,) if nb else ()
     A = torch.randn(*sh, *((K, M) if a_t else (M, K)), device="cuda").bfloat16()
     B = torch.randn(*sh, *((K, N) if b_t else (N, K)), device="cuda").bfloat16()
     Cc = G.gemm(A, B, a_t=a_t, b_t=b_t, block_n=bn, **kw)
-    for _ in range(3):
-        G.gemm(A, B, a_t=a_t, b_t=b_t, block_n=bn, out=Cc, **kw)
-    torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(iters):
-        G.gemm(A, B, a_t=a_t, b_t=b_t, block_n=bn, out=Cc, **kw)
-    e1.record()
-    torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / iters
+    ms = _graph_time(lambda: G.gemm(A, B, a_t=a_t, b_t=b_t, block_n=bn, out=Cc, **kw), iters)
     fl = 2.0 * M * N * K * max(nb, 1)
-    # cuBLAS for context
     Af = A.transpose(-1, -2) if a_t else A
     Bf = B if b_t else B.transpose(-1, -2)
-    for _ in range(3):
-        torch.matmul(Af, Bf)
-    torch.cuda.synchronize()
-    e0.record()
-    for _ in range(iters):
-        torch.matmul(Af, Bf)
-    e1.record()
-    torch.cuda.synchronize()
-    ms_ref = e0.elapsed_time(e1) / iters
+    Cr = torch.matmul(Af, Bf)
+    ms_ref = _graph_time(lambda: torch.matmul(Af, Bf, out=Cr), iters)
     log(f"bench M={M} N={N} K={K} a_t={int(a_t)} b_t={int(b_t)} bn={bn} nb={nb} {kw}: {ms*1e3:.1f} us "
         f"{fl/ms/1e9:.0f} TFLOP/s | cuBLAS {ms_ref*1e3:.1f} us {fl/ms_ref/1e9:.0f} TFLOP/s")
 
@@ -107,17 +109,22 @@ def main():
     log("ALL OK" if allok else "SOME FAILED", f"({time.time()-t0:.1f}s)")
     if not allok and os.environ.get("GEMM_BENCH_ANYWAY") != "1":
         return 1
-    for bn in (128, 256):
-        bench(4096, 2304, 768, False, False, bn)
-        bench(4096, 3072, 768, False, False, bn)
-        bench(4096, 768, 3072, False, False, bn)
-        bench(4096, 768, 768, False, False, bn)
-        bench(8192, 8192, 8192, False, False, bn)
-    bench(4096, 768, 3072, False, True, 128)
-    bench(3072, 768, 4096, True, True, 128)
-    bench(768, 768, 4096, True, True, 128, splits=4)
-    bench(512, 512, 64, False, False, 128, nb=96)
-    bench(512, 64, 512, False, True, 64, nb=96)
+    for cm in (1, 0):  # 1 = single-CTA tiles, 0 = auto (2-SM pairs)
+        log(f"--- cluster_m={cm}")
+        for bn in (128, 256):
+            bench(4096, 2304, 768, False, False, bn, cluster_m=cm)   # QKV fwd
+            bench(4096, 3072, 768, False, False, bn, cluster_m=cm)   # FFN1 fwd
+            bench(4096, 768, 3072, False, False, bn, cluster_m=cm)   # FFN2 fwd
+            bench(4096, 768, 768, False, False, bn, cluster_m=cm)    # out-proj fwd
+        bench(8192, 8192, 8192, False, False, 256, iters=5, cluster_m=cm)
+        bench(4096, 768, 3072, False, True, 256, cluster_m=cm)       # FFN1 dgrad
+        bench(4096, 3072, 768, False, True, 256, cluster_m=cm)       # FFN2 dgrad
+        bench(3072, 768, 4096, True, True, 128, cluster_m=cm)        # FFN1 wgrad
+        bench(3072, 768, 4096, True, True, 256, cluster_m=cm)
+        bench(768, 3072, 4096, True, True, 256, cluster_m=cm)        # FFN2 wgrad
+        bench(2304, 768, 4096, True, True, 256, cluster_m=cm)        # QKV wgrad
+        bench(768, 768, 4096, True, True, 128, splits=4, cluster_m=cm)
+        bench(768, 768, 4096, True, True, 256, splits=4, cluster_m=cm)
     return 0
 
 

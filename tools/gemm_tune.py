@@ -1,0 +1,97 @@
+"""Autotune (block_n, cluster_m, splits) per GEMM shape of the encoder models on the B200 and
+write ops/gemm_tuning.json.  Timing = CUDA-graph replay of 10 launches (no host overhead)."""
+import itertools
+import json
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from huggingface_sagemaker_tensorflow_distributed_b200.ops import gemm as G  # noqa: E402
+
+OUT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
+                   "huggingface_sagemaker_tensorflow_distributed_b200", "ops", "gemm_tuning.json")
+
+
+def graph_time(fn, iters=10):
+    for _ in range(2):
+        fn()
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for _ in range(iters):
+            fn()
+    g.replay()
+    torch.cuda.synchronize()
+    best = 1e9
+    for _ in range(3):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        g.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1) / iters)
+    return best * 1e3  # us
+
+
+def shapes():
+    out = []
+    for d in (768, 1024):
+        F = 4 * d
+        for M in (4096, 2048, 1024):
+            lin = [(3 * d, d), (d, d), (F, d), (d, F)]  # (out N, in K) of qkv / out / ffn1 / ffn2
+            for (N, K) in lin:
+                out.append((M, N, K, False, False))   # forward  X[M,K] · W[N,K]ᵀ
+                out.append((M, K, N, False, True))    # dgrad    dY[M,N] · W[N,K]   -> gemm(M, N=K, K=N, b_t)
+                out.append((N, K, M, True, True))     # wgrad    dYᵀ[N,M] · X[M,K]  -> gemm(M=N, N=K, K=M)
+    seen, uniq = set(), []
+    for s in out:
+        if s not in seen:
+            seen.add(s)
+            uniq.append(s)
+    return uniq
+
+
+def main():
+    table = {}
+    for (M, N, K, a_t, b_t) in shapes():
+        A = torch.randn((K, M) if a_t else (M, K), device="cuda").bfloat16()
+        B = torch.randn((K, N) if b_t else (N, K), device="cuda").bfloat16()
+        C = torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
+        wgrad = a_t and b_t
+        split_opts = (1, 2, 3, 4, 6, 8) if wgrad else (1,)
+        ws = torch.empty(M * N * 8, dtype=torch.float32, device="cuda") if wgrad else None
+        best = None
+        for bn, mc, sp in itertools.product((128, 256), (1, 2), split_opts):
+            if N % bn and N > bn and bn == 256:
+                pass
+            try:
+                us = graph_time(lambda: G.gemm(A, B, a_t=a_t, b_t=b_t, out=C, block_n=bn, cluster_m=(1 if mc == 1 else 0),
+                                               splits=sp, workspace=ws))
+            except Exception as e:  # noqa: BLE001
+                print("skip", (M, N, K, a_t, b_t), bn, mc, sp, e)
+                continue
+            if best is None or us < best[0]:
+                best = (us, bn, mc, sp)
+        Af = A.t() if a_t else A
+        Bf = B if b_t else B.t()
+        Cr = torch.matmul(Af, Bf)
+        ref = graph_time(lambda: torch.matmul(Af, Bf, out=Cr))
+        fl = 2.0 * M * N * K
+        key = f"{M},{N},{K},{int(a_t)},{int(b_t)}"
+        table[key] = {"block_n": best[1], "cluster_m": best[2], "splits": best[3], "us": round(best[0], 2),
+                      "tflops": round(fl / best[0] / 1e6, 1), "cublas_us": round(ref, 2)}
+        print(key, table[key], flush=True)
+    with open(OUT, "w") as f:
+        json.dump(table, f, indent=0, sort_keys=True)
+    os.makedirs("gpurun_out", exist_ok=True)
+    with open("gpurun_out/gemm_tuning.json", "w") as f:
+        json.dump(table, f, indent=0, sort_keys=True)
+    tot = sum(v["us"] for v in table.values())
+    ref = sum(v["cublas_us"] for v in table.values())
+    print(f"sum ours {tot:.0f} us, cuBLAS {ref:.0f} us, ratio {tot/ref:.2f}")
+
+
+if __name__ == "__main__":
+    main()
