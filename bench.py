@@ -170,6 +170,8 @@ def main() -> None:
             eng.last_step_metrics().cpu()
 
         e2e_ms, _ = timed(e2e_step, K)
+        m = eng.last_step_metrics().cpu().tolist()
+        extra["last_loss"] = m[0] / max(m[2], 1.0)
         # untimed: ~2.5 s more of the same load so the 100 ms clock sampler sees it.  The count is
         # derived from the all-reduced step time, hence identical on every rank.
         for _ in range(min(5000, int(2500.0 / max(dev_ms / K, 1e-3)) + 1)):
@@ -178,12 +180,20 @@ def main() -> None:
         clocks = sampler.stop()
         launches = plan.launches * K
         parallelism = f"dp{world}" + ("" if world == 1 else f"-{eng.dp.mode}")
-        m = eng.last_step_metrics().cpu().tolist()
-        extra["last_loss"] = m[0] / max(m[2], 1.0)
+        extra["dp"] = eng.dp.describe() if world > 1 else {"mode": "local"}
         extra["cuda_graph"] = plan.graph is not None
-        if a.exposed_comm and world > 1:
-            extra["exposed_comm_ms_per_step"] = eng.dp.measure_exposed_comm(eng, plan, K, timed) if hasattr(
-                eng.dp, "measure_exposed_comm") else None
+        if a.exposed_comm and world > 1 and eng.dp.p2p is not None:
+            # same step with the bucket kernels doing only their local optimizer work (no peer
+            # loads/stores, no flags): the difference is the communication the step still exposes
+            eng.dp.p2p.debug_no_comm = True
+            for key in [k for k in eng.plans if k[2]]:
+                del eng.plans[key]
+            for i in range(W):
+                eng.train_step(*batches[i % nb])
+            plan2 = eng.plans[(B, S, True)]
+            nocomm_ms, _ = timed(lambda i: eng._run(plan2), K)
+            extra["no_comm_ms_per_step"] = round(nocomm_ms / K, 4)
+            extra["exposed_comm_ms_per_step"] = round((dev_ms - nocomm_ms) / K, 4)
 
     h2d = 2 * B * S * 4 + B * 4
     d2h = 12 if a.impl == "ours" else 4

@@ -72,6 +72,7 @@ class TrainConfig:
     cuda_graph: bool = True
     log_every: int = 50
     metrics_jsonl: Optional[str] = None
+    save_training_state: bool = False  # also write optimizer moments + step (true resume)
     train_channel: Optional[str] = None  # SM_CHANNEL_TRAIN
     test_channel: Optional[str] = None  # SM_CHANNEL_TEST
     extra: Dict[str, Any] = field(default_factory=dict)
@@ -114,6 +115,7 @@ def build_parser(distributed: bool = True) -> argparse.ArgumentParser:
     p.add_argument("--cuda_graph", type=str2bool, default=True)
     p.add_argument("--log_every", type=int, default=50)
     p.add_argument("--metrics_jsonl", type=str, default=None)
+    p.add_argument("--save_training_state", type=str2bool, nargs="?", const=True, default=False)
     p.add_argument("--train_channel", type=str, default=env.get("SM_CHANNEL_TRAIN"))
     p.add_argument("--test_channel", type=str, default=env.get("SM_CHANNEL_TEST"))
     return p

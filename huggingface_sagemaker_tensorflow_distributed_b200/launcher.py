@@ -78,6 +78,55 @@ def parse_custom_mpi_options(opts: str) -> Dict[str, str]:
     return env
 
 
+def spawn_ranks(argv: List[str], base_env: Dict[str, str], nproc: int, port: int):
+    """Start ``nproc`` copies of ``argv`` with torchrun-style rank environment; stdout/stderr of
+    every rank is forwarded line by line, prefixed with ``[rank]`` when nproc > 1."""
+    procs: List[subprocess.Popen] = []
+    threads: List[threading.Thread] = []
+
+    def pump(rank: int, pipe) -> None:
+        for line in iter(pipe.readline, ""):
+            sys.stdout.write(f"[{rank}] {line}" if nproc > 1 else line)
+            sys.stdout.flush()
+        pipe.close()
+
+    for r in range(nproc):
+        env = dict(base_env)
+        env.update({"RANK": str(r), "LOCAL_RANK": str(r), "WORLD_SIZE": str(nproc), "LOCAL_WORLD_SIZE": str(nproc),
+                    "MASTER_ADDR": "127.0.0.1", "MASTER_PORT": str(port)})
+        p = subprocess.Popen(argv, env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True,
+                             start_new_session=True)
+        procs.append(p)
+        t = threading.Thread(target=pump, args=(r, p.stdout), daemon=True)
+        t.start()
+        threads.append(t)
+    return procs, threads
+
+
+def wait_all_or_kill(procs: List[subprocess.Popen], timeout_s: Optional[float] = None) -> int:
+    """Failure detection: the first non-zero exit (or the timeout) kills every other rank.
+    Returns the job's exit code (0 only if every rank exited 0)."""
+    t0 = time.time()
+    alive = set(range(len(procs)))
+    rc_final = 0
+    while alive:
+        for i in list(alive):
+            rc = procs[i].poll()
+            if rc is None:
+                continue
+            alive.discard(i)
+            if rc != 0 and rc_final == 0:
+                rc_final = rc
+                for j in alive:
+                    _kill_group(procs[j])
+        if timeout_s is not None and time.time() - t0 > timeout_s and alive:
+            rc_final = rc_final or 124
+            for j in alive:
+                _kill_group(procs[j])
+        time.sleep(0.05)
+    return rc_final
+
+
 class LocalEstimator:
     def __init__(self, entry_point: str, source_dir: str = "./scripts", instance_type: str = "local_gpu",
                  instance_count: int = 1, hyperparameters: Optional[Dict[str, Any]] = None,
@@ -142,26 +191,7 @@ class LocalEstimator:
             base_env.update(parse_custom_mpi_options(self.distribution["mpi"].get("custom_mpi_options", "")))
         base_env.update(self.environment)
         nproc = plan["nproc"]
-        port = _free_port()
-        procs: List[subprocess.Popen] = []
-        threads: List[threading.Thread] = []
-
-        def pump(rank: int, pipe) -> None:
-            for line in iter(pipe.readline, ""):
-                sys.stdout.write(f"[{rank}] {line}" if nproc > 1 else line)
-                sys.stdout.flush()
-            pipe.close()
-
-        for r in range(nproc):
-            env = dict(base_env)
-            env.update({"RANK": str(r), "LOCAL_RANK": str(r), "WORLD_SIZE": str(nproc), "LOCAL_WORLD_SIZE": str(nproc),
-                        "MASTER_ADDR": "127.0.0.1", "MASTER_PORT": str(port)})
-            p = subprocess.Popen(plan["argv"], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True,
-                                 start_new_session=True)
-            procs.append(p)
-            t = threading.Thread(target=pump, args=(r, p.stdout), daemon=True)
-            t.start()
-            threads.append(t)
+        procs, threads = spawn_ranks(plan["argv"], base_env, nproc, _free_port())
         self.latest_job = {"name": job_name, "dir": job_dir, "model_dir": model_dir, "output_data_dir": out_dir,
                            "procs": procs, "plan": plan}
         if not wait:
@@ -178,26 +208,7 @@ class LocalEstimator:
         return self.latest_job
 
     def _wait(self, procs: List[subprocess.Popen]) -> int:
-        """Failure detection: the first non-zero exit kills every other rank."""
-        t0 = time.time()
-        alive = set(range(len(procs)))
-        rc_final = 0
-        while alive:
-            for i in list(alive):
-                rc = procs[i].poll()
-                if rc is None:
-                    continue
-                alive.discard(i)
-                if rc != 0 and rc_final == 0:
-                    rc_final = rc
-                    for j in alive:
-                        _kill_group(procs[j])
-            if self.timeout_s is not None and time.time() - t0 > self.timeout_s and alive:
-                rc_final = rc_final or 124
-                for j in alive:
-                    _kill_group(procs[j])
-            time.sleep(0.05)
-        return rc_final
+        return wait_all_or_kill(procs, self.timeout_s)
 
 
 def _kill_group(p: subprocess.Popen) -> None:

@@ -79,6 +79,7 @@ class Plan:
     def __init__(self, B: int, S: int, train: bool):
         self.B, self.S, self.train = B, S, train
         self.ops: List[Callable[[], None]] = []
+        self.names: List[str] = []  # one label per op (profiling / NVTX)
         self.graph: Optional[torch.cuda.CUDAGraph] = None
         self.bufs: Dict[str, torch.Tensor] = {}
         self.launches = 0  # kernel launches per step (counted while recording)
@@ -168,8 +169,8 @@ class EngineBackend:
         return {"iterations": int(st.step), "m": m.cpu(), "v": v.cpu()}
 
     def load_optimizer_state(self, st: dict) -> None:
-        if not st:
-            return
+        if not st or "m" not in st:
+            return  # (a PyTorch-backend checkpoint keeps per-parameter moments; only weights carry over)
         self.dp.set_moments(st["m"].to(self.device), st["v"].to(self.device))
         self.state = K.new_step_state(self.device, seed=self.seed, step=int(st.get("iterations", 0)))
         self._metrics_view = self.state[METRICS_ACC_OFFSET:METRICS_ACC_OFFSET + 32].view(torch.float64)
@@ -235,6 +236,8 @@ class EngineBackend:
             plan.launches += 1
         plan.launches += 1
         plan.ops.append(lambda g=g, splits=splits, ws=ws: G.gemm_raw(g, None, splits, ws))
+        plan.names.append(kw.get("name") or f"gemm[{g.M}x{g.N}x{g.K}{'T' if g.a_mn_major else 'N'}{'T' if g.b_mn_major else 'N'}"
+                          f"{'/b%d' % (g.nb0 * g.nb1) if g.nb0 * g.nb1 > 1 else ''}]")
 
     def _linear_fwd(self, plan, x, w_name, out, M, epilogue=G.EPI_NONE, aux=None):
         w = self.W(w_name + ".weight")
@@ -255,6 +258,7 @@ class EngineBackend:
             db = self.Gr(w_name + ".bias")
             plan.launches += 2
             plan.ops.append(lambda dy=dy, db=db, part=part: K.colsum(dy, db, part))
+            plan.names.append("colsum(bias grad)")
         if dx is not None:
             self._gemm_op(plan, A=dy, B=w, C=dx, lda=N, ldb=Kd, ldc=Kd, M=M, N=Kd, K=N, b_t=True, epilogue=epilogue,
                           aux=aux, ldaux=ldaux)
@@ -323,9 +327,15 @@ class EngineBackend:
         eps = cfg.layer_norm_eps
         sref = st if train else None
 
-        def op(fn, n_launch=1):
+        def op(fn, n_launch=1, name=None):
             plan.launches += n_launch
             plan.ops.append(fn)
+            if name is None:  # label = first kernel-wrapper name referenced by the lambda
+                co = fn.__code__.co_names
+                name = next((n for n in co if n in ("step_prologue", "position_ids", "ln_fwd", "ln_bwd", "softmax_fwd",
+                                                    "softmax_bwd", "attn_fwd", "attn_bwd", "head_fwd", "head_bwd",
+                                                    "embed_bwd", "colsum", "zero_")), "op")
+            plan.names.append(name)
 
         if train:
             o = self.opt
@@ -518,6 +528,14 @@ class EngineBackend:
 
     def launches_per_step(self, B: int, S: int, train: bool = True) -> int:
         return self._get_plan(B, S, train).launches
+
+    def profile(self, B: int, S: int, train: bool = True, repeats: int = 5):
+        """Per-op device time of one step (eager, CUDA events): [(name, calls, us)]."""
+        from ..utils.timers import profile_ops
+
+        plan = self._get_plan(B, S, train)
+        names = plan.names + ["dp/optimizer"] * (len(plan.ops) - len(plan.names))
+        return profile_ops(plan.ops, names, repeats)
 
     def finish(self) -> None:
         torch.cuda.synchronize()

@@ -28,6 +28,7 @@ class TorchBackend:
         torch.random.set_rng_state(gen_state)
         self.optimizer: Optional[KerasAdamW] = None
         self.distributed = False
+        self._pending_opt_state: Optional[dict] = None
 
     # ---- state ------------------------------------------------------------------
     def state_dict(self) -> Dict[str, torch.Tensor]:
@@ -51,7 +52,10 @@ class TorchBackend:
         return {"iterations": self.optimizer.iterations, "state": st}
 
     def load_optimizer_state(self, st: dict) -> None:
-        if not st or self.optimizer is None:
+        if not st:
+            return
+        if self.optimizer is None:  # applied as soon as the optimizer is bound (setup_training)
+            self._pending_opt_state = st
             return
         self.optimizer.iterations = int(st.get("iterations", 0))
         for n, p in self.model.named_parameters():
@@ -74,6 +78,9 @@ class TorchBackend:
     def setup_training(self, opt: Adam, total_steps: int, batch_size: int, seq_len: int) -> None:
         self.optimizer = opt.bind(self.model.parameters(), total_steps)
         self.distributed = bool(opt.distributed) and comm.size() > 1
+        if self._pending_opt_state is not None:
+            st, self._pending_opt_state = self._pending_opt_state, None
+            self.load_optimizer_state(st)
 
     def _forward(self, feats, labels, train: bool):
         ids = feats["input_ids"].to(self.device, non_blocking=True).long()

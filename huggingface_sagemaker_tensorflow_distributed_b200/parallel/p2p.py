@@ -242,8 +242,13 @@ class P2PGroup:
 
     def record_bucket(self, plan, bucket, state, master, m, v, overlap: bool = True) -> None:
         mode = self.modes[bucket.index]
-        _, _, off = self.owned[bucket.index]
-        args = self.make_args(bucket.index, bucket.start, bucket.numel, mode, True, state, master, m, v, off)
+        start_o, n_o, off = self.owned[bucket.index]
+        if getattr(self, "debug_no_comm", False):
+            # timing aid for the "exposed communication" metric: the same optimizer work on the
+            # owned slice, but no peer traffic and no cross-rank flags (ranks diverge: never train so)
+            args = self.make_args(bucket.index, start_o, n_o, AR_LOCAL, True, state, master, m, v, off)
+        else:
+            args = self.make_args(bucket.index, bucket.start, bucket.numel, mode, True, state, master, m, v, off)
         plan.launches += 1
         if not overlap:
             plan.ops.append(lambda args=args: self.launch(args))

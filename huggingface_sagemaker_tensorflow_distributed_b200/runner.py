@@ -74,5 +74,5 @@ def train_eval_save(cfg: TrainConfig, model, train_ds, test_ds, logger, *, callb
                 logger.info("  %s = %s", k, v)
             T.write_eval_results(os.path.join(cfg.output_data_dir, "eval_results.txt"), result)
     # unconditional, as in the reference (scripts/train.py:182-183) — but rank 0 + barrier
-    model.save_pretrained(cfg.model_dir)
+    model.save_pretrained(cfg.model_dir, save_training_state=cfg.save_training_state)
     return out

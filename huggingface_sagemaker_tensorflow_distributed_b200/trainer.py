@@ -243,6 +243,9 @@ class AutoModelForSequenceClassification:
             sd = checkpoint.load_pretrained_state(name_or_path, cfg)
             if sd is not None:
                 be.load_state_dict(sd)
+            ts = checkpoint.load_training_state(name_or_path)  # true resume: Adam moments + step counter
+            if ts is not None:
+                be.load_optimizer_state(ts["optimizer"])
         from .data import try_load_tokenizer
 
         return SequenceClassifier(cfg, be, tokenizer=try_load_tokenizer(name_or_path))

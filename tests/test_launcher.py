@@ -79,3 +79,33 @@ def test_one_dead_rank_kills_the_job(tmp_path):
     with pytest.raises(RuntimeError, match="exited with code 3"):
         est.fit()
     assert time.time() - t0 < 20
+
+
+def test_mirrored_strategy_single_command_fans_out_to_replicas(tmp_path):
+    """singe_node_train.py with 2 (CPU stand-in) devices: one command, two replica processes,
+    global batch split in two, one set of result files (reference scripts/singe_node_train.py)."""
+    import subprocess
+    repo = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    wrapper = tmp_path / "run.py"
+    wrapper.write_text(textwrap.dedent(f"""
+        import os, sys, runpy
+        sys.path.insert(0, {repo!r})
+        os.environ["HSTD_FORCE_CPU"] = "1"
+        import huggingface_sagemaker_tensorflow_distributed_b200.parallel.mirrored as M
+        _orig = M.MirroredStrategy.__init__
+        def _init(self, devices=None):
+            _orig(self, devices if devices is not None else ["cpu", "cpu"])
+        M.MirroredStrategy.__init__ = _init
+        sys.argv = [{os.path.join(repo, 'scripts', 'singe_node_train.py')!r}] + sys.argv[1:]
+        runpy.run_path(sys.argv[0], run_name="__main__")
+    """))
+    env = dict(os.environ, SM_OUTPUT_DATA_DIR=str(tmp_path / "out"), SM_MODEL_DIR=str(tmp_path / "model"),
+               OMP_NUM_THREADS="1")
+    r = subprocess.run([sys.executable, str(wrapper), "--model_name_or_path", "tiny-distilbert", "--epochs", "1",
+                        "--train_batch_size", "8", "--max_seq_length", "16", "--train_samples", "32", "--test_samples",
+                        "8", "--log_every", "0"], env=env, capture_output=True, text=True, timeout=280)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "[0]" in r.stdout and "[1]" in r.stdout and "replica 1 of 2" in r.stdout
+    assert sorted(os.listdir(tmp_path / "out")) == ["eval_results.txt", "train_results.txt"]
+    assert "train_runtime" not in open(tmp_path / "out" / "train_results.txt").read()
+    assert sorted(os.listdir(tmp_path / "model")) == ["config.json", "model.safetensors"]

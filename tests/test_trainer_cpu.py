@@ -104,3 +104,26 @@ def test_two_rank_gloo_equals_one_rank_with_double_batch(tmp_path):
     ref = model.state_dict()
     for k in ref:
         assert torch.allclose(ref[k], sd0[k], atol=2e-5), k
+
+
+def test_true_resume_with_optimizer_state(tmp_path):
+    """2 steps + save(training state) + reload + 2 steps == 4 steps straight (beyond the
+    reference, whose only resume is weights via --model_name_or_path)."""
+    ds = None
+    def run(model, batches):
+        model.compile(optimizer=Adam(learning_rate=1e-3))
+        model.backend.setup_training(model.optimizer, 100, 4, 16)
+        for feats, labels in batches:
+            model.backend.train_step(feats, labels)
+    base = _tiny(seed=3)
+    ds = list(BatchedDataset(synthetic_imdb(base.cfg, 16, 16), 4))
+    run(base, ds)
+    straight = base.state_dict()
+    first = _tiny(seed=3)
+    run(first, ds[:2])
+    first.save_pretrained(str(tmp_path), save_training_state=True)
+    assert "training_state.pt" in os.listdir(tmp_path)
+    resumed = T.AutoModelForSequenceClassification.from_pretrained(str(tmp_path), device=torch.device("cpu"), dropout=0.0)
+    run(resumed, ds[2:])
+    for k, v in straight.items():
+        assert torch.allclose(resumed.state_dict()[k], v, atol=1e-6), k
