@@ -105,7 +105,7 @@ __global__ void __launch_bounds__(LN_WARPS * 32) ln_fwd_kernel(const hstd_ln_arg
 // ------------------------------------------------------------------ LayerNorm backward
 // partials layout: [gridDim.x][3][d] floats (dgamma, dbeta, dbias)
 template <int NV>
-__global__ void __launch_bounds__(LN_WARPS * 32) ln_bwd_kernel(const hstd_ln_bwd_args p) {
+__global__ void __launch_bounds__(LN_WARPS * 32, 2) ln_bwd_kernel(const hstd_ln_bwd_args p) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int d = p.d;
   const Dropout din = make_dropout(p.state, p.p_in, p.site_in);

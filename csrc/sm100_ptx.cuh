@@ -225,11 +225,42 @@ __host__ __device__ constexpr uint32_t make_idesc_bf16(int M, int N, bool a_mn_m
 }
 
 // ---------------------------------------------------------------- misc math
-__device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
+__device__ __forceinline__ float rcp_approx(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+// Exact-erf GELU for GEMM epilogues in ~16 instructions and 2 MUFU ops per element (libdevice
+// erff costs 3-4x that and made the FFN GEMMs epilogue-bound).  erf via Abramowitz & Stegun
+// 7.1.26, |error| <= 3e-7 — far below bf16 resolution: with z = |x|/sqrt(2), t = 1/(1 + p z):
+//   erfc(z) = (a1 t + a2 t^2 + a3 t^3 + a4 t^4 + a5 t^5) * exp(-z^2).
+// exp(-z^2) = exp(-x^2/2) is also the Gaussian factor of the derivative, so GELU' needs no
+// second exponential.
+__device__ __forceinline__ void gelu_parts(float x, float& cdf, float& e) {
+  const float z = fabsf(x) * 0.70710678118654752f;
+  const float t = rcp_approx(fmaf(0.3275911f, z, 1.0f));
+  e = ex2_approx(z * z * -1.4426950408889634f);
+  float poly = fmaf(1.061405429f, t, -1.453152027f);
+  poly = fmaf(poly, t, 1.421413741f);
+  poly = fmaf(poly, t, -0.284496736f);
+  poly = fmaf(poly, t, 0.254829592f);
+  const float half_erfc = 0.5f * poly * t * e;          // 0.5 * erfc(z)
+  cdf = x >= 0.f ? 1.0f - half_erfc : half_erfc;        // Phi(x)
+}
+__device__ __forceinline__ float gelu_erf(float x) {
+  float cdf, e;
+  gelu_parts(x, cdf, e);
+  return x * cdf;
+}
 __device__ __forceinline__ float gelu_erf_grad(float x) {
-  const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752f));
-  const float pdf = 0.3989422804014327f * __expf(-0.5f * x * x);
-  return cdf + x * pdf;
+  float cdf, e;
+  gelu_parts(x, cdf, e);
+  return fmaf(x * 0.3989422804014327f, e, cdf);          // Phi(x) + x * phi(x)
 }
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
