@@ -231,7 +231,9 @@ extern "C" HSTD_API int64_t hstd_allreduce_flag_words(int num_buckets) {
 
 extern "C" HSTD_API int hstd_fused_allreduce(const hstd_allreduce_args* a, void* stream) {
   if (a->world < 1 || a->world > AR_MAX_WORLD) return set_error(-1, "allreduce: bad world size");
-  if (a->numel % (8 * a->world) != 0) return set_error(-1, "allreduce: bucket size must be a multiple of 8*world");
+  const bool local_only = a->mode == HSTD_AR_LOCAL || a->world == 1;
+  if (a->numel % (local_only ? 8 : 8 * a->world) != 0)
+    return set_error(-1, "allreduce: bucket size must be a multiple of 8*world (8 for the local update)");
   if (a->start % 8 != 0) return set_error(-1, "allreduce: bucket start must be a multiple of 8");
   ArKernelParams p;
   for (int r = 0; r < AR_MAX_WORLD; ++r) {
