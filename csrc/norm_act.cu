@@ -103,89 +103,111 @@ __global__ void __launch_bounds__(LN_WARPS * 32) ln_fwd_kernel(const hstd_ln_arg
 }
 
 // ------------------------------------------------------------------ LayerNorm backward
-// partials layout: [gridDim.x][3][d] floats (dgamma, dbeta, dbias)
+// Two passes over the same (L2-resident) data instead of one register-heavy kernel:
+//   rows kernel: one warp per row, dpre = LN'(dropout_out'(dy)), da = dropout_in'(dpre);
+//   cols kernel: threads own 8 columns and walk the rows: dgamma, dbeta, dbias partials.
+// (A single fused kernel needs 72 column accumulators per lane on top of the row data: 201
+// registers -> 8 warps per SM and 1.3 TB/s; the split runs both halves at high occupancy.)
 template <int NV>
-__global__ void __launch_bounds__(LN_WARPS * 32, 2) ln_bwd_kernel(const hstd_ln_bwd_args p) {
+__global__ void __launch_bounds__(LN_WARPS * 32) ln_bwd_rows_kernel(const hstd_ln_bwd_args p) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * LN_WARPS + warp;
+  if (row >= p.M) return;
   const int d = p.d;
   const Dropout din = make_dropout(p.state, p.p_in, p.site_in);
   const Dropout dout = make_dropout(p.state, p.p_out, p.site_out);
   const __nv_bfloat16* gamma = static_cast<const __nv_bfloat16*>(p.gamma);
-  float g[NV][8];
+  const float mean = p.mean[row], rstd = p.rstd[row];
+  float gd[NV][8], xh[NV][8];
+  float s1 = 0.f, s2 = 0.f;
 #pragma unroll
-  for (int i = 0; i < NV; ++i) load8(gamma + i * 256 + lane * 8, g[i]);
-  float acc_g[NV][8], acc_b[NV][8], acc_a[NV][8];
+  for (int i = 0; i < NV; ++i) {
+    const int col = i * 256 + lane * 8;
+    float g[8];
+    load8(static_cast<const __nv_bfloat16*>(p.dy) + int64_t(row) * d + col, gd[i]);
+    load8(static_cast<const __nv_bfloat16*>(p.pre) + int64_t(row) * d + col, xh[i]);
+    load8(gamma + col, g);
+    if (dout.active()) {
+      float m[8];
+      dropout_mask8(dout, (uint64_t(row) * d + col) >> 3, m);
 #pragma unroll
-  for (int i = 0; i < NV; ++i)
-#pragma unroll
-    for (int j = 0; j < 8; ++j) acc_g[i][j] = acc_b[i][j] = acc_a[i][j] = 0.f;
-
-  for (int row = blockIdx.x * LN_WARPS + warp; row < p.M; row += gridDim.x * LN_WARPS) {
-    const float mean = p.mean[row], rstd = p.rstd[row];
-    float dy[NV][8], xh[NV][8];
-    float s1 = 0.f, s2 = 0.f;
-#pragma unroll
-    for (int i = 0; i < NV; ++i) {
-      const int col = i * 256 + lane * 8;
-      load8(static_cast<const __nv_bfloat16*>(p.dy) + int64_t(row) * d + col, dy[i]);
-      if (dout.active()) {
-        float m[8];
-        dropout_mask8(dout, (uint64_t(row) * d + col) >> 3, m);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) dy[i][j] *= m[j];
-      }
-      load8(static_cast<const __nv_bfloat16*>(p.pre) + int64_t(row) * d + col, xh[i]);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        xh[i][j] = (xh[i][j] - mean) * rstd;
-        const float gd = g[i][j] * dy[i][j];
-        s1 += gd;
-        s2 += gd * xh[i][j];
-        acc_g[i][j] += dy[i][j] * xh[i][j];
-        acc_b[i][j] += dy[i][j];
-      }
+      for (int j = 0; j < 8; ++j) gd[i][j] *= m[j];
     }
-    s1 = warp_sum(s1) / float(d);
-    s2 = warp_sum(s2) / float(d);
 #pragma unroll
-    for (int i = 0; i < NV; ++i) {
-      const int col = i * 256 + lane * 8;
-      float dp[8];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) dp[j] = rstd * (g[i][j] * dy[i][j] - s1 - xh[i][j] * s2);
-      store8(static_cast<__nv_bfloat16*>(p.dpre) + int64_t(row) * d + col, dp);
-      if (p.da != nullptr) {
-        if (din.active()) {
-          float m[8];
-          dropout_mask8(din, (uint64_t(row) * d + col) >> 3, m);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) dp[j] *= m[j];
-        }
-        store8(static_cast<__nv_bfloat16*>(p.da) + int64_t(row) * d + col, dp);
-      }
-#pragma unroll
-      for (int j = 0; j < 8; ++j) acc_a[i][j] += bf16_round(dp[j]);
+    for (int j = 0; j < 8; ++j) {
+      xh[i][j] = (xh[i][j] - mean) * rstd;
+      gd[i][j] *= g[j];
+      s1 += gd[i][j];
+      s2 += gd[i][j] * xh[i][j];
     }
   }
+  s1 = warp_sum(s1) / float(d);
+  s2 = warp_sum(s2) / float(d);
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int col = i * 256 + lane * 8;
+    float dp[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) dp[j] = rstd * (gd[i][j] - s1 - xh[i][j] * s2);
+    store8(static_cast<__nv_bfloat16*>(p.dpre) + int64_t(row) * d + col, dp);
+    if (p.da != nullptr) {
+      if (din.active()) {
+        float m[8];
+        dropout_mask8(din, (uint64_t(row) * d + col) >> 3, m);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) dp[j] *= m[j];
+      }
+      store8(static_cast<__nv_bfloat16*>(p.da) + int64_t(row) * d + col, dp);
+    }
+  }
+}
 
-  // block reduction over the LN_WARPS warps, one quantity at a time through smem
-  __shared__ float red[LN_WARPS][NV * 256];
-  float* out = p.partials + int64_t(blockIdx.x) * 3 * d;
+// partials layout: [gridDim.y][3][d] floats (dgamma, dbeta, dbias); grid (d/256, LN_COL_ROWGROUPS)
+constexpr int LN_COL_ROWGROUPS = 32;
+__global__ void __launch_bounds__(256) ln_bwd_cols_kernel(const hstd_ln_bwd_args p) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int d = p.d;
+  const int col = blockIdx.x * 256 + lane * 8;
+  const Dropout dout = make_dropout(p.state, p.p_out, p.site_out);
+  const __nv_bfloat16* src_a = static_cast<const __nv_bfloat16*>(p.da ? p.da : p.dpre);
+  float ag[8], ab[8], aa[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) ag[j] = ab[j] = aa[j] = 0.f;
+  for (int row = blockIdx.y * 8 + warp; row < p.M; row += gridDim.y * 8) {
+    const float mean = p.mean[row], rstd = p.rstd[row];
+    float dy[8], x[8], a[8];
+    load8(static_cast<const __nv_bfloat16*>(p.dy) + int64_t(row) * d + col, dy);
+    load8(static_cast<const __nv_bfloat16*>(p.pre) + int64_t(row) * d + col, x);
+    load8(src_a + int64_t(row) * d + col, a);
+    if (dout.active()) {
+      float m[8];
+      dropout_mask8(dout, (uint64_t(row) * d + col) >> 3, m);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) dy[j] *= m[j];
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      ag[j] += dy[j] * (x[j] - mean) * rstd;
+      ab[j] += dy[j];
+      aa[j] += a[j];
+    }
+  }
+  __shared__ float red[3][8][256];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    red[0][warp][lane * 8 + j] = ag[j];
+    red[1][warp][lane * 8 + j] = ab[j];
+    red[2][warp][lane * 8 + j] = aa[j];
+  }
+  __syncthreads();
+  const int c = threadIdx.x;
+  float* out = p.partials + int64_t(blockIdx.y) * 3 * d + blockIdx.x * 256 + c;
 #pragma unroll
   for (int q = 0; q < 3; ++q) {
+    float s = 0.f;
 #pragma unroll
-    for (int i = 0; i < NV; ++i)
-#pragma unroll
-      for (int j = 0; j < 8; ++j)
-        red[warp][i * 256 + lane * 8 + j] = (q == 0 ? acc_g[i][j] : (q == 1 ? acc_b[i][j] : acc_a[i][j]));
-    __syncthreads();
-    for (int c = threadIdx.x; c < d; c += LN_WARPS * 32) {
-      float s = 0.f;
-#pragma unroll
-      for (int w = 0; w < LN_WARPS; ++w) s += red[w][c];
-      out[q * d + c] = s;
-    }
-    __syncthreads();
+    for (int w = 0; w < 8; ++w) s += red[q][w][c];
+    out[q * d] = s;
   }
 }
 
@@ -435,14 +457,15 @@ extern "C" HSTD_API int hstd_ln_bwd(const hstd_ln_bwd_args* a, void* stream) {
   if (int rc = check_d(a->d, "ln_bwd")) return rc;
   if (!a->partials) return set_error(-1, "ln_bwd: partials scratch is required");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  int blocks = (a->M + LN_WARPS - 1) / LN_WARPS;
-  if (blocks > LN_BWD_MAX_BLOCKS) blocks = LN_BWD_MAX_BLOCKS;
-  HSTD_DISPATCH_NV(a->d / 256, ln_bwd_kernel<NV><<<blocks, LN_WARPS * 32, 0, s>>>(*a));
-  if (int rc = check_launch("ln_bwd")) return rc;
+  const int blocks = (a->M + LN_WARPS - 1) / LN_WARPS;
+  HSTD_DISPATCH_NV(a->d / 256, ln_bwd_rows_kernel<NV><<<blocks, LN_WARPS * 32, 0, s>>>(*a));
+  if (int rc = check_launch("ln_bwd rows")) return rc;
+  ln_bwd_cols_kernel<<<dim3(a->d / 256, LN_COL_ROWGROUPS), 256, 0, s>>>(*a);
+  if (int rc = check_launch("ln_bwd cols")) return rc;
   const int width = 3 * a->d;
   partials_finalize_kernel<<<(width + FIN_COLS - 1) / FIN_COLS, FIN_COLS * FIN_GROUPS, 0, s>>>(
-      a->partials, blocks, width, a->d, static_cast<__nv_bfloat16*>(a->dgamma), static_cast<__nv_bfloat16*>(a->dbeta),
-      static_cast<__nv_bfloat16*>(a->dbias));
+      a->partials, LN_COL_ROWGROUPS, width, a->d, static_cast<__nv_bfloat16*>(a->dgamma),
+      static_cast<__nv_bfloat16*>(a->dbeta), static_cast<__nv_bfloat16*>(a->dbias));
   return check_launch("ln_bwd finalize");
 }
 

@@ -336,6 +336,8 @@ class EngineBackend:
                                                     "softmax_bwd", "attn_fwd", "attn_bwd", "head_fwd", "head_bwd",
                                                     "embed_bwd", "colsum", "zero_")), "op")
             plan.names.append(name)
+            if name == "ln_bwd":
+                plan.launches += 1  # rows + cols + finalize
 
         if train:
             o = self.opt
