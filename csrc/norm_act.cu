@@ -163,7 +163,7 @@ __global__ void __launch_bounds__(LN_WARPS * 32) ln_bwd_rows_kernel(const hstd_l
 }
 
 // partials layout: [gridDim.y][3][d] floats (dgamma, dbeta, dbias); grid (d/256, LN_COL_ROWGROUPS)
-constexpr int LN_COL_ROWGROUPS = 32;
+constexpr int LN_COL_ROWGROUPS = 96;  // 3 x 96 = 288 blocks at d = 768: two per SM
 __global__ void __launch_bounds__(256) ln_bwd_cols_kernel(const hstd_ln_bwd_args p) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int d = p.d;
@@ -238,7 +238,8 @@ partials_finalize_kernel(const float* __restrict__ partials, int nparts, int wid
 }
 
 // ------------------------------------------------------------------ column sums
-constexpr int COLSUM_ROWGROUPS = 32;
+constexpr int COLSUM_ROWGROUPS = 32;       // built-in-scratch entry point (512 KiB for N <= 4096)
+constexpr int COLSUM_ROWGROUPS_WS = 96;    // caller-workspace entry point: more blocks in flight
 __global__ void __launch_bounds__(256) colsum_partial_kernel(const __nv_bfloat16* __restrict__ x, int64_t ld, int M,
                                                              int N, float* __restrict__ partials) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -469,16 +470,16 @@ extern "C" HSTD_API int hstd_ln_bwd(const hstd_ln_bwd_args* a, void* stream) {
   return check_launch("ln_bwd finalize");
 }
 
-extern "C" HSTD_API int64_t hstd_colsum_partials_floats(int N) { return int64_t(COLSUM_ROWGROUPS) * N; }
+extern "C" HSTD_API int64_t hstd_colsum_partials_floats(int N) { return int64_t(COLSUM_ROWGROUPS_WS) * N; }
 
 extern "C" HSTD_API int hstd_colsum(const void* x, int64_t ld, int M, int N, void* out, float* partials, void* stream) {
   if (N % 8 != 0) return set_error(-1, "colsum: N must be a multiple of 8");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  dim3 grid((N + 255) / 256, COLSUM_ROWGROUPS);
+  dim3 grid((N + 255) / 256, COLSUM_ROWGROUPS_WS);
   colsum_partial_kernel<<<grid, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(x), ld, M, N, partials);
   if (int rc = check_launch("colsum")) return rc;
-  partials_finalize_kernel<<<(N + FIN_COLS - 1) / FIN_COLS, FIN_COLS * FIN_GROUPS, 0, s>>>(partials, COLSUM_ROWGROUPS, N, N,
-                                                           static_cast<__nv_bfloat16*>(out), nullptr, nullptr);
+  partials_finalize_kernel<<<(N + FIN_COLS - 1) / FIN_COLS, FIN_COLS * FIN_GROUPS, 0, s>>>(
+      partials, COLSUM_ROWGROUPS_WS, N, N, static_cast<__nv_bfloat16*>(out), nullptr, nullptr);
   return check_launch("colsum finalize");
 }
 
