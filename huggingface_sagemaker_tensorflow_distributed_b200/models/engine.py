@@ -82,6 +82,7 @@ class Plan:
         self.names: List[str] = []  # one label per op (profiling / NVTX)
         self.graph: Optional[torch.cuda.CUDAGraph] = None
         self.bufs: Dict[str, torch.Tensor] = {}
+        self.keep: list = []  # events referenced by recorded ops
         self.launches = 0  # kernel launches per step (counted while recording)
         self.warm = 0
 
@@ -91,7 +92,7 @@ class EngineBackend:
 
     def __init__(self, cfg: EncoderConfig, device: torch.device, seed: int = 42, bucket_mb: float = 32.0,
                  comm_mode: str = "p2p", use_cuda_graph: bool = True, overlap: bool = True,
-                 fused_attention: bool = True):
+                 fused_attention: bool = True, dual_stream: bool = True):
         if device.type != "cuda":
             raise RuntimeError("EngineBackend needs a CUDA device")
         _lib.load()  # fail loudly if libhstd_b200.so is missing: no silent eager fallback
@@ -103,6 +104,9 @@ class EngineBackend:
         self.use_cuda_graph = use_cuda_graph
         self.bucket_mb, self.comm_mode, self.overlap = bucket_mb, comm_mode, overlap
         self.fused_attention = fused_attention
+        # weight-gradient GEMMs run on a second stream, concurrently with the dgrad chain
+        self.dual_stream = dual_stream
+        self.side_stream = torch.cuda.Stream(device=device) if dual_stream else None
         self.seed = seed
         self.world, self.rank = comm.size(), comm.rank()
 
@@ -245,20 +249,67 @@ class EngineBackend:
         self._gemm_op(plan, A=x, B=w, C=out, bias=self.W(w_name + ".bias"), lda=Kd, ldb=Kd, ldc=N, M=M, N=N, K=Kd,
                       epilogue=epilogue, aux=aux, ldaux=N)
 
+    def _on_side(self, plan, first: int) -> None:
+        """Re-home the ops recorded since index ``first`` onto the side stream: they start once
+        everything recorded on the main stream so far has finished (event fork)."""
+        if not self.dual_stream:
+            return
+        side = self.side_stream
+        ev = torch.cuda.Event()
+        plan.keep.append(ev)
+        moved = plan.ops[first:]
+        del plan.ops[first:]
+        names = plan.names[first:]
+        del plan.names[first:]
+
+        def fork(ev=ev):
+            ev.record(torch.cuda.current_stream())
+            side.wait_event(ev)
+
+        plan.ops.append(fork)
+        plan.names.append("fork")
+        for f, n in zip(moved, names):
+            def run(f=f):
+                with torch.cuda.stream(side):
+                    f()
+            plan.ops.append(run)
+            plan.names.append(n + "@side")
+        plan.side_dirty = True
+
+    def _join_side(self, plan) -> None:
+        """Main stream waits for everything queued on the side stream so far."""
+        if not self.dual_stream or not getattr(plan, "side_dirty", False):
+            return
+        side = self.side_stream
+        ev = torch.cuda.Event()
+        plan.keep.append(ev)
+
+        def join(ev=ev):
+            ev.record(side)
+            torch.cuda.current_stream().wait_event(ev)
+
+        plan.ops.append(join)
+        plan.names.append("join")
+        plan.side_dirty = False
+
     def _linear_bwd(self, plan, dy, x, w_name, dx, M, *, epilogue=G.EPI_NONE, aux=None, ldaux=0, bias_grad=True):
-        """dW = dyᵀ·x ; db = colsum(dy) (unless fused elsewhere) ; dx = dy·W (+ epilogue)."""
+        """dW = dyᵀ·x ; db = colsum(dy) (unless fused elsewhere) ; dx = dy·W (+ epilogue).
+        dW / db do not feed the rest of backward, so they go to the side stream."""
         w = self.W(w_name + ".weight")
         N, Kd = w.shape  # forward: [M,Kd] x [N,Kd]ᵀ
         tiles = ((N + 127) // 128) * ((Kd + 127) // 128)
         splits = max(1, min(8, round(148 / tiles), M // 512))
+        first = len(plan.ops)
         self._gemm_op(plan, A=dy, B=x, C=self.Gr(w_name + ".weight"), lda=N, ldb=Kd, ldc=Kd, M=N, N=Kd, K=M, a_t=True,
                       b_t=True, splits=splits)
         if bias_grad:
-            part = self._shared("colsum_partials", K.colsum_partials_floats(N))
+            # one scratch per stream: main-stream colsums (token-type grads) must not share it
+            part = self._shared("colsum_partials_side", K.colsum_partials_floats(N))
             db = self.Gr(w_name + ".bias")
             plan.launches += 2
             plan.ops.append(lambda dy=dy, db=db, part=part: K.colsum(dy, db, part))
             plan.names.append("colsum(bias grad)")
+        self._on_side(plan, first)
         if dx is not None:
             self._gemm_op(plan, A=dy, B=w, C=dx, lda=N, ldb=Kd, ldc=Kd, M=M, N=Kd, K=N, b_t=True, epilogue=epilogue,
                           aux=aux, ldaux=ldaux)
@@ -404,7 +455,7 @@ class EngineBackend:
 
         # ---------------------------------------------------------------- backward
         op(lambda: K.head_bwd(hargs), 4)
-        bufA, bufB, bufC = (self._buf(plan, n, (M, d)) for n in ("gA", "gB", "gC"))
+        bufA, bufB, bufC, bufD = (self._buf(plan, n, (M, d)) for n in ("gA", "gB", "gC", "gD"))
         dctx = self._buf(plan, "dctx", (M, d))
         du = self._buf(plan, "du", (M, F))
         dP = None if fused else self._buf(plan, "dP", (B, H, S, S))
@@ -427,10 +478,12 @@ class EngineBackend:
                              bias_grad=False)
             # FFN1: dW1, db1, dh1 = du·W1 + d(r2)
             self._linear_bwd(plan, du, h1[i], pfx + "ffn1", bufC, M, epilogue=G.EPI_ADD, aux=bufA, ldaux=d)
+            if self.dp.wants_early_buckets():
+                self._join_side(plan)
             self.dp.after_grads(plan, [pfx + n for n in ("ln2.weight", "ln2.bias", "ffn2.weight", "ffn2.bias",
                                                           "ffn1.weight", "ffn1.bias")])
             # LN1 backward: dh1 (C) -> d(r1) in A ; dropout' -> B
-            da1 = bufB if p_attn_out > 0 else None
+            da1 = bufD if p_attn_out > 0 else None  # (bufB may still be read by the FFN2 wgrad on the side stream)
             op(lambda i=i, da1=da1: K.ln_bwd(dy=bufC, pre=r1[i], mean=mean1[i], rstd=rstd1[i],
                                              gamma=self.W(f"layers.{i}.ln1.weight"), dpre=bufA, da=da1,
                                              dgamma=self.Gr(f"layers.{i}.ln1.weight"), dbeta=self.Gr(f"layers.{i}.ln1.bias"),
@@ -445,6 +498,8 @@ class EngineBackend:
                 self._attention_bwd_unfused(plan, i, qkv, Pd, P, dP, dctx, dqkv, B, S, H, dh, d, scale, p_att, st, op)
             # QKV projection: dWqkv, dbqkv, dx = dqkv·Wqkv + d(r1)
             self._linear_bwd(plan, dqkv, x_in[i], pfx + "qkv", dx, M, epilogue=G.EPI_ADD, aux=bufA, ldaux=d)
+            # the next layer overwrites the gradient buffers the side stream is still reading
+            self._join_side(plan)
             self.dp.after_grads(plan, [pfx + n for n in ("ln1.weight", "ln1.bias", "out.weight", "out.bias",
                                                           "qkv.weight", "qkv.bias")])
         # embeddings
@@ -461,6 +516,7 @@ class EngineBackend:
         names = ["emb.ln.weight", "emb.ln.bias", "emb.pos.weight", "emb.word.weight"]
         if cfg.type_vocab_size > 0:
             names.append("emb.tok_type.weight")
+        self._join_side(plan)
         self.dp.after_grads(plan, names)
         self.dp.end_backward(plan)
         return plan

@@ -95,6 +95,10 @@ class DPEngine:
     def configure(self, distributed: bool) -> None:
         self.distributed = distributed and self.world > 1
 
+    def wants_early_buckets(self) -> bool:
+        """True when a bucket can be reduced as soon as its gradients exist (distributed p2p)."""
+        return self.p2p is not None and self.distributed
+
     def capturable(self) -> bool:
         return not (self.distributed and self.mode == "nccl")
 
