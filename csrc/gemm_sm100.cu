@@ -42,6 +42,7 @@ struct GemmKernelParams {
   int num_splits, kb_per_split;
   int epilogue;
   float alpha;
+  int use_tma_store;  // bf16 output through smem staging + TMA bulk stores (BN >= 128, no split-K)
 };
 
 // Per-CTA smem: with MC == 2 (cta_group::2) each CTA of the pair stages only half of the B tile.
@@ -49,8 +50,9 @@ template <int BN, int MC>
 struct GemmCfg {
   static constexpr uint32_t A_BYTES = BLOCK_M * BLOCK_K * 2;
   static constexpr uint32_t B_BYTES = (BN / MC) * BLOCK_K * 2;
-  static constexpr int STAGES = (200 * 1024) / int(A_BYTES + B_BYTES) > 8 ? 8 : (200 * 1024) / int(A_BYTES + B_BYTES);
-  static constexpr size_t SMEM = 1024 /*align slack*/ + size_t(STAGES) * (A_BYTES + B_BYTES) + 256;
+  static constexpr int STAGES = (192 * 1024) / int(A_BYTES + B_BYTES) > 8 ? 8 : (192 * 1024) / int(A_BYTES + B_BYTES);
+  static constexpr uint32_t STAGING_BYTES = NUM_EPI_WARPS * 4096;  // per warp: 32 rows x 128 B for the TMA store
+  static constexpr size_t SMEM = 1024 /*align slack*/ + size_t(STAGES) * (A_BYTES + B_BYTES) + STAGING_BYTES + 256;
 };
 
 // MC = CTAs per tile along M.  MC == 2 is the 2-SM form (cta_group::2): a cluster of two CTAs
@@ -61,6 +63,7 @@ struct GemmCfg {
 template <int BN, bool A_MN, bool B_MN, int MC>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                 const __grid_constant__ CUtensorMap tmap_c, const __grid_constant__ CUtensorMap tmap_aux,
                  const GemmKernelParams p) {
   constexpr int STAGES = GemmCfg<BN, MC>::STAGES;
   constexpr uint32_t A_BYTES = GemmCfg<BN, MC>::A_BYTES;
@@ -74,7 +77,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + STAGES * A_BYTES;
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_b + STAGES * B_BYTES);
+  uint8_t* smem_stage = smem_b + STAGES * B_BYTES;  // epilogue store staging, 4 KiB per warp
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_stage + GemmCfg<BN, MC>::STAGING_BYTES);
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tmem_full = empty_bar + STAGES;
   uint64_t* tmem_empty = tmem_full + 2;
@@ -88,6 +92,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_b);
+    if (p.use_tma_store) tma_prefetch_desc(&tmap_c);
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&full_bar[s], 1);   // MC == 2: only the leader's copy is used
       mbar_init(&empty_bar[s], 1);
@@ -253,12 +258,109 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       tc_fence_after();
       const uint32_t t_row = tmem_base + acc * BN + col_half * COLS_PER_WARP + (uint32_t(quarter * 32) << 16);
       const int64_t zoff = int64_t(z0) * p.c_bs0 + int64_t(z1) * p.c_bs1;
+      if constexpr (BN >= 128) {
+        if (p.use_tma_store) {
+          // Coalesced path: 32 rows x 64 columns at a time go through a 128B-swizzled smem tile
+          // and leave with one TMA bulk store (full 128-byte lines; rows/cols past M/N are clipped
+          // by the tensor map).  Direct per-lane stores touch 32 rows x 16 B per instruction and
+          // ran at a third of the HBM write bandwidth.
+          uint8_t* stage = smem_stage + ew * 4096;
+          const int row0 = tm * BLOCK_M + quarter * 32;
+#pragma unroll 1
+          for (int g = 0; g < COLS_PER_WARP; g += 64) {
+            const int col0 = col_base + g;
+            float f[64];
+            {
+              uint32_t v0[32], v1[32];
+              tmem_ld_32x32(t_row + g, v0);
+              tmem_ld_32x32(t_row + g + 32, v1);
+              tmem_ld_wait();
+#pragma unroll
+              for (int j = 0; j < 32; ++j) {
+                f[j] = __uint_as_float(v0[j]) * p.alpha;
+                f[32 + j] = __uint_as_float(v1[j]) * p.alpha;
+              }
+            }
+            const bool in_range = row < p.M && col0 < p.N;  // (N is a multiple of 8; finer column clipping is the TMA's)
+            if (p.bias != nullptr) {
+#pragma unroll
+              for (int j = 0; j < 64; j += 8) {
+                if (col0 + j < p.N) {
+                  const uint4 b = __ldg(reinterpret_cast<const uint4*>(p.bias + col0 + j));
+                  const float2 b0 = unpack_bf16x2(b.x), b1 = unpack_bf16x2(b.y), b2 = unpack_bf16x2(b.z),
+                               b3 = unpack_bf16x2(b.w);
+                  f[j] += b0.x; f[j + 1] += b0.y; f[j + 2] += b1.x; f[j + 3] += b1.y;
+                  f[j + 4] += b2.x; f[j + 5] += b2.y; f[j + 6] += b3.x; f[j + 7] += b3.y;
+                }
+              }
+            }
+            auto flush = [&](const CUtensorMap* tm_out) {
+              if (lane == 0) tma_store_wait_read();  // previous store has drained this staging tile
+              __syncwarp();
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const uint4 o = make_uint4(pack_bf16x2(f[8 * j], f[8 * j + 1]), pack_bf16x2(f[8 * j + 2], f[8 * j + 3]),
+                                           pack_bf16x2(f[8 * j + 4], f[8 * j + 5]), pack_bf16x2(f[8 * j + 6], f[8 * j + 7]));
+                *reinterpret_cast<uint4*>(stage + lane * 128 + ((j ^ (lane & 7)) << 4)) = o;
+              }
+              fence_proxy_async_smem();
+              __syncwarp();
+              if (lane == 0) {
+                tma_store_4d(tm_out, stage, col0, row0, z0, z1);
+                tma_store_commit();
+              }
+            };
+            if (p.epilogue == HSTD_EPI_GELU) {
+              if (p.aux) flush(&tmap_aux);  // pre-activation
+#pragma unroll
+              for (int j = 0; j < 64; ++j) f[j] = gelu_erf(f[j]);
+            } else if (p.epilogue == HSTD_EPI_ADD || p.epilogue == HSTD_EPI_GELU_BWD) {
+              if (in_range) {
+                const __nv_bfloat16* auxrow = p.aux + zoff + int64_t(row) * p.ldaux + col0;
+#pragma unroll
+                for (int j = 0; j < 64; j += 8) {
+                  if (col0 + j < p.N) {
+                    const uint4 a = *reinterpret_cast<const uint4*>(auxrow + j);
+                    const float2 a0 = unpack_bf16x2(a.x), a1 = unpack_bf16x2(a.y), a2 = unpack_bf16x2(a.z),
+                                 a3 = unpack_bf16x2(a.w);
+                    if (p.epilogue == HSTD_EPI_ADD) {
+                      f[j] += a0.x; f[j + 1] += a0.y; f[j + 2] += a1.x; f[j + 3] += a1.y;
+                      f[j + 4] += a2.x; f[j + 5] += a2.y; f[j + 6] += a3.x; f[j + 7] += a3.y;
+                    } else {
+                      f[j] *= gelu_erf_grad(a0.x); f[j + 1] *= gelu_erf_grad(a0.y);
+                      f[j + 2] *= gelu_erf_grad(a1.x); f[j + 3] *= gelu_erf_grad(a1.y);
+                      f[j + 4] *= gelu_erf_grad(a2.x); f[j + 5] *= gelu_erf_grad(a2.y);
+                      f[j + 6] *= gelu_erf_grad(a3.x); f[j + 7] *= gelu_erf_grad(a3.y);
+                    }
+                  }
+                }
+              }
+            }
+            flush(&tmap_c);
+          }
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) {
+            if (MC == 1 || leader) mbar_arrive(&tmem_empty[acc]);
+            else mbar_arrive_cluster(mapa_shared(smem_u32(&tmem_empty[acc]), 0));
+          }
+          if (++acc == 2) {
+            acc = 0;
+            acc_phase ^= 1;
+          }
+          continue;
+        }
+      }
 #pragma unroll 1
       for (int c = 0; c < COLS_PER_WARP; c += 32) {
         uint32_t v[32];
         tmem_ld_32x32(t_row + c, v);
         tmem_ld_wait();
         const int col0 = col_base + c;
+        if (p.epilogue >= 100) {  // timing experiments only: 100 = no global stores
+          if (v[0] == 0x7fc12345u) p.C[0] = __float2bfloat16(1.f);
+          continue;
+        }
         if (row < p.M && col0 < p.N) {
           if (p.num_splits > 1) {
             float* dst = p.Cf32 + (int64_t(split) * p.M + row) * p.N + col0;
@@ -352,6 +454,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     }
   }
 
+  if (warp >= 2 && lane == 0) tma_store_wait_all();  // this thread's bulk stores have landed
   tc_fence_before();
   __syncthreads();
   if constexpr (MC > 1) cluster_sync_all();  // no CTA leaves while its peer may still touch its smem / barriers / TMEM
@@ -392,8 +495,8 @@ int num_sms() {
 }
 
 template <int BN, bool A_MN, bool B_MN, int MC>
-static int launch_gemm_mc(const CUtensorMap& ta, const CUtensorMap& tb, const GemmKernelParams& p, int max_ctas,
-                          cudaStream_t stream) {
+static int launch_gemm_mc(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const CUtensorMap& tx,
+                          const GemmKernelParams& p, int max_ctas, cudaStream_t stream) {
   auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, MC>;
   constexpr size_t smem = GemmCfg<BN, MC>::SMEM;
   static bool configured = false;
@@ -419,16 +522,16 @@ static int launch_gemm_mc(const CUtensorMap& ta, const CUtensorMap& tb, const Ge
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb, p);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, tx, p);
   if (e != cudaSuccess) return set_error(-6, std::string("gemm launch: ") + cudaGetErrorString(e));
   return 0;
 }
 
 template <int BN, bool A_MN, bool B_MN>
-static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmKernelParams& p, int max_ctas, int mc,
-                       cudaStream_t stream) {
-  if (mc == 2) return launch_gemm_mc<BN, A_MN, B_MN, 2>(ta, tb, p, max_ctas, stream);
-  return launch_gemm_mc<BN, A_MN, B_MN, 1>(ta, tb, p, max_ctas, stream);
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const CUtensorMap& tx,
+                       const GemmKernelParams& p, int max_ctas, int mc, cudaStream_t stream) {
+  if (mc == 2) return launch_gemm_mc<BN, A_MN, B_MN, 2>(ta, tb, tc, tx, p, max_ctas, stream);
+  return launch_gemm_mc<BN, A_MN, B_MN, 1>(ta, tb, tc, tx, p, max_ctas, stream);
 }
 
 static int pick_block_n(int M, int N, int batches, int splits) {
@@ -481,13 +584,25 @@ static int gemm_impl(const hstd_gemm_args* a, int splits, float* workspace, cuda
   p.alpha = a->alpha;
   if ((a->epilogue == HSTD_EPI_ADD || a->epilogue == HSTD_EPI_GELU_BWD) && a->aux == nullptr)
     return set_error(-1, "gemm: this epilogue needs aux");
+  // Output tensor maps (TMA bulk stores of 64-column x 32-row tiles).
+  CUtensorMap tc = ta, tx = ta;  // placeholders when unused
+  p.use_tma_store = (bn >= 128 && splits == 1 && a->epilogue < 100 && (a->ldc % 8) == 0 &&
+                     (reinterpret_cast<uintptr_t>(a->C) & 15) == 0) ? 1 : 0;
+  if (p.use_tma_store) {
+    rc = get_tmap(&tc, a->C, a->N, a->M, nb0, nb1, a->ldc, a->c_bs0, a->c_bs1, 32);
+    if (rc) return rc;
+    if (a->epilogue == HSTD_EPI_GELU && a->aux != nullptr) {
+      rc = get_tmap(&tx, a->aux, a->N, a->M, nb0, nb1, a->ldaux, a->c_bs0, a->c_bs1, 32);
+      if (rc) return rc;
+    }
+  }
 
 #define HSTD_GEMM_CASE(BN_)                                                                         \
   if (bn == BN_) {                                                                                  \
-    if (!a->a_mn_major && !a->b_mn_major) return launch_gemm<BN_, false, false>(ta, tb, p, a->max_ctas, mc, stream); \
-    if (!a->a_mn_major && a->b_mn_major) return launch_gemm<BN_, false, true>(ta, tb, p, a->max_ctas, mc, stream);   \
-    if (a->a_mn_major && !a->b_mn_major) return launch_gemm<BN_, true, false>(ta, tb, p, a->max_ctas, mc, stream);   \
-    return launch_gemm<BN_, true, true>(ta, tb, p, a->max_ctas, mc, stream);                            \
+    if (!a->a_mn_major && !a->b_mn_major) return launch_gemm<BN_, false, false>(ta, tb, tc, tx, p, a->max_ctas, mc, stream); \
+    if (!a->a_mn_major && a->b_mn_major) return launch_gemm<BN_, false, true>(ta, tb, tc, tx, p, a->max_ctas, mc, stream);   \
+    if (a->a_mn_major && !a->b_mn_major) return launch_gemm<BN_, true, false>(ta, tb, tc, tx, p, a->max_ctas, mc, stream);   \
+    return launch_gemm<BN_, true, true>(ta, tb, tc, tx, p, a->max_ctas, mc, stream);                            \
   }
   HSTD_GEMM_CASE(64)
   HSTD_GEMM_CASE(128)
