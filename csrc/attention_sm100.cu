@@ -156,15 +156,18 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
       for (int c = 0; c < nc; ++c) tma_load_4d(sK + c * TILE_BYTES, &tm_k, bar_qk, 0, c * TILE, h, b);
       mbar_expect_tx(bar_v, nc * TILE_BYTES);
       for (int c = 0; c < nc; ++c) tma_load_4d(sV + c * TILE_BYTES, &tm_v, bar_v, 0, c * TILE, h, b);
+      // descriptors once; per-MMA variation is a constant added to the 16-byte-unit address field
+      // (rebuilding them per instruction cost the single issuing thread ~100 cycles per MMA)
+      const uint64_t dq0 = make_smem_desc_sw128(smem_u32(sQ), 16, 1024);
+      const uint64_t dk0 = make_smem_desc_sw128(smem_u32(sK), 16, 1024);
+      const uint64_t dv0 = make_smem_desc_sw128(smem_u32(sV), TILE_BYTES, 1024);
+      const uint64_t dp0 = make_smem_desc_sw128(smem_u32(sP), 16, 1024);
       mbar_wait(bar_qk, 0);
       tc_fence_after();
-      const uint32_t q_addr = smem_u32(sQ);
       for (int c = 0; c < nc; ++c) {
-        const uint32_t k_addr = smem_u32(sK + c * TILE_BYTES);
+        const uint64_t dk = dk0 + uint64_t(c) * (TILE_BYTES >> 4);
 #pragma unroll
-        for (int k = 0; k < DH / 16; ++k)
-          umma_bf16(tmem + c * TILE, make_smem_desc_sw128(q_addr + k * 32, 16, 1024),
-                    make_smem_desc_sw128(k_addr + k * 32, 16, 1024), IDESC_S, k > 0);
+        for (int k = 0; k < DH / 16; ++k) umma_bf16(tmem + c * TILE, dq0 + k * 2, dk + k * 2, IDESC_S, k > 0);
         umma_commit(&bar_s[c]);
       }
       mbar_wait(bar_v, 0);
@@ -172,12 +175,11 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
         const int buf = c & 1;
         mbar_wait(&bar_p[buf], (c >> 1) & 1);
         tc_fence_after();
-        const uint32_t p_addr = smem_u32(sP + buf * P_BYTES);
-        const uint32_t v_addr = smem_u32(sV + c * TILE_BYTES);
+        const uint64_t dp = dp0 + uint64_t(buf) * (P_BYTES >> 4);
+        const uint64_t dv = dv0 + uint64_t(c) * (TILE_BYTES >> 4);
 #pragma unroll
         for (int k = 0; k < TILE / 16; ++k)
-          umma_bf16(tmem, make_smem_desc_sw128(p_addr + (k >> 2) * TILE_BYTES + (k & 3) * 32, 16, 1024),
-                    make_smem_desc_sw128(v_addr + k * 2048, TILE_BYTES, 1024), IDESC_O, (c > 0 || k > 0));
+          umma_bf16(tmem, dp + (k >> 2) * (TILE_BYTES >> 4) + (k & 3) * 2, dv + k * (2048 >> 4), IDESC_O, (c > 0 || k > 0));
         umma_commit(&bar_pfree[buf]);
       }
       umma_commit(bar_o);
@@ -380,21 +382,26 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
         tma_load_4d(sDO + i * TILE_BYTES, &tm_do, &bar_q[i], 0, i * TILE, h, b);
       }
       mbar_wait(bar_kv, 0);
-      const uint32_t k_addr = smem_u32(sK), v_addr = smem_u32(sV);
-      const uint32_t pd_addr = smem_u32(sPd), ds_addr = smem_u32(sDS);
+      // descriptors once; per-MMA variation is a constant added to the 16-byte-unit address field
+      const uint64_t dK_k = make_smem_desc_sw128(smem_u32(sK), 16, 1024);           // K as K-major B (Q·Kᵀ)
+      const uint64_t dK_mn = make_smem_desc_sw128(smem_u32(sK), TILE_BYTES, 1024);  // K as MN-major B (dS·K)
+      const uint64_t dV_k = make_smem_desc_sw128(smem_u32(sV), 16, 1024);           // V as K-major B (dO·Vᵀ)
+      const uint64_t dPd_mn = make_smem_desc_sw128(smem_u32(sPd), TILE_BYTES, 1024);
+      const uint64_t dDS_mn = make_smem_desc_sw128(smem_u32(sDS), TILE_BYTES, 1024);
+      const uint64_t dDS_k = make_smem_desc_sw128(smem_u32(sDS), 16, 1024);
+      const uint64_t dQ_k0 = make_smem_desc_sw128(smem_u32(sQ), 16, 1024);
+      const uint64_t dQ_mn0 = make_smem_desc_sw128(smem_u32(sQ), TILE_BYTES, 1024);
+      const uint64_t dDO_k0 = make_smem_desc_sw128(smem_u32(sDO), 16, 1024);
+      const uint64_t dDO_mn0 = make_smem_desc_sw128(smem_u32(sDO), TILE_BYTES, 1024);
       for (int i = 0; i < NQ; ++i) {
         const int buf = i & 1;
+        const uint64_t boff = uint64_t(buf) * (TILE_BYTES >> 4);
         mbar_wait(&bar_q[buf], (i >> 1) & 1);
         tc_fence_after();
-        const uint32_t q_addr = smem_u32(sQ + buf * TILE_BYTES), do_addr = smem_u32(sDO + buf * TILE_BYTES);
 #pragma unroll
-        for (int k = 0; k < DH / 16; ++k)
-          umma_bf16(tmem + C_S, make_smem_desc_sw128(q_addr + k * 32, 16, 1024),
-                    make_smem_desc_sw128(k_addr + k * 32, 16, 1024), IDESC_S, k > 0);
+        for (int k = 0; k < DH / 16; ++k) umma_bf16(tmem + C_S, dQ_k0 + boff + k * 2, dK_k + k * 2, IDESC_S, k > 0);
 #pragma unroll
-        for (int k = 0; k < DH / 16; ++k)
-          umma_bf16(tmem + C_DP, make_smem_desc_sw128(do_addr + k * 32, 16, 1024),
-                    make_smem_desc_sw128(v_addr + k * 32, 16, 1024), IDESC_S, k > 0);
+        for (int k = 0; k < DH / 16; ++k) umma_bf16(tmem + C_DP, dDO_k0 + boff + k * 2, dV_k + k * 2, IDESC_S, k > 0);
         umma_commit(bar_sdp);
         mbar_wait(bar_pds, i & 1);
         tc_fence_after();
@@ -405,17 +412,14 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
         // reduction over the 128 query rows of this tile: 8 k-steps of 16 rows = 2048 B each
 #pragma unroll
         for (int k = 0; k < TILE / 16; ++k)
-          umma_bf16(tmem + C_DV, make_smem_desc_sw128(pd_addr + k * 2048, TILE_BYTES, 1024),
-                    make_smem_desc_sw128(do_addr + k * 2048, TILE_BYTES, 1024), IDESC_T, (i > 0 || k > 0));
+          umma_bf16(tmem + C_DV, dPd_mn + k * (2048 >> 4), dDO_mn0 + boff + k * (2048 >> 4), IDESC_T, (i > 0 || k > 0));
 #pragma unroll
         for (int k = 0; k < TILE / 16; ++k)
-          umma_bf16(tmem + C_DK, make_smem_desc_sw128(ds_addr + k * 2048, TILE_BYTES, 1024),
-                    make_smem_desc_sw128(q_addr + k * 2048, TILE_BYTES, 1024), IDESC_T, (i > 0 || k > 0));
+          umma_bf16(tmem + C_DK, dDS_mn + k * (2048 >> 4), dQ_mn0 + boff + k * (2048 >> 4), IDESC_T, (i > 0 || k > 0));
         // dQ_i = dS · K : reduction over the 128 keys (dS K-major: 4 k-steps per 64-key atom)
 #pragma unroll
         for (int k = 0; k < TILE / 16; ++k)
-          umma_bf16(tmem + C_DQ, make_smem_desc_sw128(ds_addr + (k >> 2) * TILE_BYTES + (k & 3) * 32, 16, 1024),
-                    make_smem_desc_sw128(k_addr + k * 2048, TILE_BYTES, 1024), IDESC_Q, k > 0);
+          umma_bf16(tmem + C_DQ, dDS_k + (k >> 2) * (TILE_BYTES >> 4) + (k & 3) * 2, dK_mn + k * (2048 >> 4), IDESC_Q, k > 0);
         umma_commit(bar_dq);
         mbar_wait(bar_dq, i & 1);  // tiles Q/dO[buf], Pd, dS are free again
         if (i + 2 < NQ) {

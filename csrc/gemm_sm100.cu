@@ -194,6 +194,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
+      const uint64_t desc_a0 = A_MN ? make_smem_desc_sw128(smem_u32(smem_a), 64 * BLOCK_K * 2, 1024)
+                                    : make_smem_desc_sw128(smem_u32(smem_a), 16, 1024);
+      const uint64_t desc_b0 = B_MN ? make_smem_desc_sw128(smem_u32(smem_b), 64 * BLOCK_K * 2, 1024)
+                                    : make_smem_desc_sw128(smem_u32(smem_b), 16, 1024);
       for (int tile = first_tile; tile < total_tiles; tile += tile_stride) {
         int r = tile % tiles_per_batch;
         const int split = r / (tiles_mp * p.tiles_n);
@@ -205,16 +209,16 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         for (int kb = kb_begin; kb < kb_end; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
-          const uint32_t a_addr = smem_u32(smem_a + stage * A_BYTES);
-          const uint32_t b_addr = smem_u32(smem_b + stage * B_BYTES);
+          // descriptors: stage base + constant per-k-step increments (in 16-byte units); building
+          // them from scratch costs ~50 dependent instructions per MMA on the single issuing thread
+          const uint64_t da0 = desc_a0 + uint64_t(stage) * (A_BYTES >> 4);
+          const uint64_t db0 = desc_b0 + uint64_t(stage) * (B_BYTES >> 4);
 #pragma unroll
           for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
             // K-major: advance 16 elements (32 B) inside the swizzled row.
             // MN-major: advance 16 K-rows = two 8-row groups of 1024 B.
-            const uint64_t da = A_MN ? make_smem_desc_sw128(a_addr + k * 2048, 64 * BLOCK_K * 2, 1024)
-                                     : make_smem_desc_sw128(a_addr + k * 32, 16, 1024);
-            const uint64_t db = B_MN ? make_smem_desc_sw128(b_addr + k * 2048, 64 * BLOCK_K * 2, 1024)
-                                     : make_smem_desc_sw128(b_addr + k * 32, 16, 1024);
+            const uint64_t da = da0 + uint64_t(k * (A_MN ? 2048 / 16 : 32 / 16));
+            const uint64_t db = db0 + uint64_t(k * (B_MN ? 2048 / 16 : 32 / 16));
             if constexpr (MC == 1) umma_bf16(d_tmem, da, db, IDESC, (kb > kb_begin || k > 0) ? 1u : 0u);
             else umma_bf16_2sm(d_tmem, da, db, IDESC, (kb > kb_begin || k > 0) ? 1u : 0u);
           }
