@@ -150,7 +150,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
     if (sBits[w] != 0) nc = (w >> 2) + 1;
 
   if (warp == AT_SOFTMAX_WARPS) {
-    if (lane == 0) {
+    if (elect_one()) {
       mbar_expect_tx(bar_qk, (1 + nc) * TILE_BYTES);
       tma_load_4d(sQ, &tm_q, bar_qk, 0, qt * TILE, h, b);
       for (int c = 0; c < nc; ++c) tma_load_4d(sK + c * TILE_BYTES, &tm_k, bar_qk, 0, c * TILE, h, b);
@@ -372,7 +372,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
   const uint32_t tmem = *tmem_slot;
 
   if (warp == AT_SOFTMAX_WARPS) {
-    if (lane == 0) {
+    if (elect_one()) {
       mbar_expect_tx(bar_kv, 2 * TILE_BYTES);
       tma_load_4d(sK, &tm_k, bar_kv, 0, kt * TILE, h, b);
       tma_load_4d(sV, &tm_v, bar_kv, 0, kt * TILE, h, b);

@@ -43,7 +43,9 @@ struct GemmKernelParams {
   int epilogue;
   float alpha;
   int use_tma_store;  // bf16 output through smem staging + TMA bulk stores (BN >= 128, no split-K)
+  long long* trace;   // optional clock64() stamps of CTA 0 (tools/gemm_trace.py); null in production
 };
+#define HSTD_GTRACE(slot) do { if (p.trace && blockIdx.x == 0 && (slot) < 512) p.trace[slot] = clock64(); } while (0)
 
 // Per-CTA smem: with MC == 2 (cta_group::2) each CTA of the pair stages only half of the B tile.
 template <int BN, int MC>
@@ -86,6 +88,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) HSTD_GTRACE(0);
   const int cta_rank = MC > 1 ? int(cluster_ctarank()) : 0;
   const bool leader = cta_rank == 0;
 
@@ -126,7 +129,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer (every CTA)
-    if (lane == 0) {
+    if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = first_tile; tile < total_tiles; tile += tile_stride) {
@@ -142,6 +145,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         const int kb_end = min(num_kb_total, kb_begin + p.kb_per_split);
         for (int kb = kb_begin; kb < kb_end; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
+          HSTD_GTRACE(2 + 4 * (kb - kb_begin) + 0);  // producer: slot free
           uint8_t* sa = smem_a + stage * A_BYTES;
           uint8_t* sb = smem_b + stage * B_BYTES;
           const int k0 = kb * BLOCK_K;
@@ -189,7 +193,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer (leader CTA only)
-    if (lane == 0 && leader) {
+    if (leader && elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
@@ -207,7 +211,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
         for (int kb = kb_begin; kb < kb_end; ++kb) {
+          HSTD_GTRACE(2 + 4 * (kb - kb_begin) + 1);  // mma: starts waiting for data
           mbar_wait(&full_bar[stage], phase);
+          HSTD_GTRACE(2 + 4 * (kb - kb_begin) + 2);  // mma: data landed
           tc_fence_after();
           // descriptors: stage base + constant per-k-step increments (in 16-byte units); building
           // them from scratch costs ~50 dependent instructions per MMA on the single issuing thread
@@ -222,6 +228,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             if constexpr (MC == 1) umma_bf16(d_tmem, da, db, IDESC, (kb > kb_begin || k > 0) ? 1u : 0u);
             else umma_bf16_2sm(d_tmem, da, db, IDESC, (kb > kb_begin || k > 0) ? 1u : 0u);
           }
+          HSTD_GTRACE(2 + 4 * (kb - kb_begin) + 3);  // mma: k-block issued
           // smem stage free once these MMAs retire (in both CTAs of a pair)
           if constexpr (MC == 1) umma_commit(&empty_bar[stage]);
           else umma_commit_2sm(&empty_bar[stage], PAIR_MASK);
@@ -538,6 +545,8 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUten
   return launch_gemm_mc<BN, A_MN, B_MN, 1>(ta, tb, tc, tx, p, max_ctas, stream);
 }
 
+static long long* g_gemm_trace = nullptr;
+
 static int pick_block_n(int M, int N, int batches, int splits) {
   // 256-wide tiles halve the B-operand smem traffic per FLOP; use them when they still
   // give every SM a tile, otherwise fall back to 128 (64 for the narrow attention outputs).
@@ -586,6 +595,7 @@ static int gemm_impl(const hstd_gemm_args* a, int splits, float* workspace, cuda
   p.kb_per_split = (num_kb + splits - 1) / splits;
   p.epilogue = a->epilogue;
   p.alpha = a->alpha;
+  p.trace = g_gemm_trace;
   if ((a->epilogue == HSTD_EPI_ADD || a->epilogue == HSTD_EPI_GELU_BWD) && a->aux == nullptr)
     return set_error(-1, "gemm: this epilogue needs aux");
   // Output tensor maps (TMA bulk stores of 64-column x 32-row tiles).
@@ -616,6 +626,12 @@ static int gemm_impl(const hstd_gemm_args* a, int splits, float* workspace, cuda
 }
 
 }  // namespace hstd
+
+// Debug aid: device buffer of >= 512 int64 that CTA 0 of the following GEMM launches fills with
+// clock64() stamps of its producer / MMA threads per k-block (NULL switches it off).
+extern "C" HSTD_API void hstd_gemm_set_trace(void* device_buffer) {
+  hstd::g_gemm_trace = static_cast<long long*>(device_buffer);
+}
 
 extern "C" HSTD_API int hstd_gemm_bf16(const hstd_gemm_args* args, void* stream) {
   return hstd::gemm_impl(args, 1, nullptr, static_cast<cudaStream_t>(stream));
