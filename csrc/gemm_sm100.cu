@@ -306,7 +306,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
               }
             }
             auto flush = [&](const CUtensorMap* tm_out) {
-              if (lane == 0) tma_store_wait_read();  // previous store has drained this staging tile
+              // (elect.sync picks the same lane for the same member mask, so the thread that waits
+              // on the bulk group is the one that committed it)
+              if (elect_one()) tma_store_wait_read();  // previous store has drained this staging tile
               __syncwarp();
 #pragma unroll
               for (int j = 0; j < 8; ++j) {
@@ -316,7 +318,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
               }
               fence_proxy_async_smem();
               __syncwarp();
-              if (lane == 0) {
+              if (elect_one()) {
                 tma_store_4d(tm_out, stage, col0, row0, z0, z1);
                 tma_store_commit();
               }
@@ -465,7 +467,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     }
   }
 
-  if (warp >= 2 && lane == 0) tma_store_wait_all();  // this thread's bulk stores have landed
+  if (warp >= 2) {
+    __syncwarp();
+    if (elect_one()) tma_store_wait_all();  // this thread's bulk stores have landed
+  }
   tc_fence_before();
   __syncthreads();
   if constexpr (MC > 1) cluster_sync_all();  // no CTA leaves while its peer may still touch its smem / barriers / TMEM
