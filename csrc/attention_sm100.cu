@@ -102,6 +102,7 @@ template <int NC>
 __global__ void __launch_bounds__(AT_THREADS, 1)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
                 const __grid_constant__ CUtensorMap tm_v, const AttnParams p) {
+  HSTD_PDL_PROLOGUE();
   constexpr uint32_t TMEM_COLS = NC == 1 ? 128 : (NC == 2 ? 256 : 512);
   constexpr uint32_t IDESC_S = make_idesc_bf16(TILE, TILE, false, false);
   constexpr uint32_t IDESC_O = make_idesc_bf16(TILE, DH, false, true);
@@ -287,6 +288,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
 __global__ void __launch_bounds__(256) attn_delta_kernel(const __nv_bfloat16* __restrict__ dO,
                                                          const __nv_bfloat16* __restrict__ O, float* __restrict__ delta,
                                                          int B, int S, int H) {
+  HSTD_PDL_PROLOGUE();
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp >= B * S) return;
   const int b = warp / S, q = warp - b * S;
@@ -310,6 +312,7 @@ __global__ void __launch_bounds__(AT_THREADS, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
                 const __grid_constant__ CUtensorMap tm_v, const __grid_constant__ CUtensorMap tm_do,
                 const AttnParams p) {
+  HSTD_PDL_PROLOGUE();
   constexpr uint32_t TMEM_COLS = 512;
   constexpr uint32_t C_S = 0, C_DP = 128, C_DV = 256, C_DK = 320, C_DQ = 384;
   constexpr uint32_t IDESC_S = make_idesc_bf16(TILE, TILE, false, false);   // Q·Kᵀ, dO·Vᵀ
@@ -522,6 +525,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
 __global__ void __launch_bounds__(256) attn_dq_reduce_kernel(const __nv_bfloat16* __restrict__ part,
                                                              __nv_bfloat16* __restrict__ dqkv, int64_t M, int d,
                                                              int nparts) {
+  HSTD_PDL_PROLOGUE();
   const int64_t nvec = M * d / 8;
   for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < nvec; i += int64_t(gridDim.x) * blockDim.x) {
     float acc[8];
@@ -586,7 +590,7 @@ extern "C" HSTD_API int hstd_attn_fwd(const void* qkv, void* ctx, float* lse, co
       if (int rc = set_smem(attn_fwd_kernel<NC_>, fwd_smem(NC_))) return rc;      \
       configured[NC_] = true;                                                     \
     }                                                                             \
-    attn_fwd_kernel<NC_><<<grid, AT_THREADS, fwd_smem(NC_), s>>>(tq, tk, tv, p);  \
+    launch_pdl(attn_fwd_kernel<NC_>, grid, dim3(AT_THREADS), fwd_smem(NC_), s, tq, tk, tv, p);  \
     break;                                                                        \
   }
   switch (nc) {
@@ -614,8 +618,8 @@ extern "C" HSTD_API int hstd_attn_bwd(const void* qkv, const void* ctx, const vo
   __nv_bfloat16* dq_part = reinterpret_cast<__nv_bfloat16*>(static_cast<uint8_t*>(workspace) + int64_t(B) * H * S * 4);
   const __nv_bfloat16* base = static_cast<const __nv_bfloat16*>(qkv);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  attn_delta_kernel<<<unsigned((M * 32 + 255) / 256), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(dctx),
-                                                                    static_cast<const __nv_bfloat16*>(ctx), delta, B, S, H);
+  launch_pdl(attn_delta_kernel, dim3(unsigned((M * 32 + 255) / 256)), dim3(256), 0, s,
+             static_cast<const __nv_bfloat16*>(dctx), static_cast<const __nv_bfloat16*>(ctx), delta, B, S, H);
   if (int rc = check_launch("attn_delta")) return rc;
   CUtensorMap tq, tk, tv, tdo;
   if (int rc = get_tmap(&tq, base, DH, S, H, B, 3 * d, DH, S * 3 * d, TILE)) return rc;
@@ -639,7 +643,7 @@ extern "C" HSTD_API int hstd_attn_bwd(const void* qkv, const void* ctx, const vo
       if (int rc = set_smem(attn_bwd_kernel<NQ_>, bwd_smem())) return rc;              \
       configured[NQ_] = true;                                                          \
     }                                                                                  \
-    attn_bwd_kernel<NQ_><<<grid, AT_THREADS, bwd_smem(), s>>>(tq, tk, tv, tdo, p);     \
+    launch_pdl(attn_bwd_kernel<NQ_>, grid, dim3(AT_THREADS), bwd_smem(), s, tq, tk, tv, tdo, p);     \
     break;                                                                             \
   }
   switch (nq) {
@@ -650,6 +654,7 @@ extern "C" HSTD_API int hstd_attn_bwd(const void* qkv, const void* ctx, const vo
   if (int rc = check_launch("attn_bwd")) return rc;
   int blocks = int((M * d / 8 + 255) / 256);
   if (blocks > 148 * 8) blocks = 148 * 8;
-  attn_dq_reduce_kernel<<<blocks, 256, 0, s>>>(dq_part, static_cast<__nv_bfloat16*>(dqkv), M, int(d), nq);
+  launch_pdl(attn_dq_reduce_kernel, dim3(blocks), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(dq_part),
+             static_cast<__nv_bfloat16*>(dqkv), M, int(d), nq);
   return check_launch("attn_dq_reduce");
 }

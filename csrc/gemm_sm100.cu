@@ -120,6 +120,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   if constexpr (MC > 1) cluster_sync_all();  // peer barriers are initialised before anything remote lands
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // PDL: everything above (barrier init, TMEM allocation, descriptor prefetch) overlapped the
+  // previous kernel's tail; from here on we read and write global memory.
+  pdl_launch_dependents();
+  pdl_wait();
 
   const int tiles_mp = (p.tiles_m + MC - 1) / MC;  // M tiles are handed out in groups of MC
   const int tiles_per_batch = tiles_mp * p.tiles_n * p.num_splits;
@@ -484,6 +488,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 // fp32 split-K partials -> bf16
 __global__ void splitk_reduce_kernel(const float* __restrict__ ws, __nv_bfloat16* __restrict__ C, int64_t ldc, int M,
                                      int N, int splits, float alpha) {
+  HSTD_PDL_PROLOGUE();
   const int64_t n4 = int64_t(M) * N / 4;
   for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n4; i += int64_t(gridDim.x) * blockDim.x) {
     float4 s = reinterpret_cast<const float4*>(ws)[i];
@@ -531,13 +536,15 @@ static int launch_gemm_mc(const CUtensorMap& ta, const CUtensorMap& tb, const CU
   cfg.blockDim = dim3(GEMM_THREADS);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = MC;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = pdl_enabled() ? 2 : 1;
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, tx, p);
   if (e != cudaSuccess) return set_error(-6, std::string("gemm launch: ") + cudaGetErrorString(e));
   return 0;
@@ -666,9 +673,9 @@ extern "C" HSTD_API int hstd_gemm_bf16_splitk(const hstd_gemm_args* args, int sp
   const int64_t n4 = int64_t(args->M) * args->N / 4;
   int blocks = int((n4 + 255) / 256);
   if (blocks > 148 * 8) blocks = 148 * 8;
-  splitk_reduce_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const float*>(workspace), static_cast<__nv_bfloat16*>(args->C), args->ldc, args->M, args->N, splits,
-      args->alpha);
+  launch_pdl(splitk_reduce_kernel, dim3(blocks), dim3(256), 0, static_cast<cudaStream_t>(stream),
+             static_cast<const float*>(workspace), static_cast<__nv_bfloat16*>(args->C), args->ldc, args->M, args->N, splits,
+             args->alpha);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return set_error(-6, std::string("splitk reduce launch: ") + cudaGetErrorString(e));
   return 0;

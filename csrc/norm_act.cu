@@ -22,6 +22,7 @@ constexpr int LN_BWD_MAX_BLOCKS = 296;  // 2 per SM
 // ------------------------------------------------------------------ LayerNorm forward
 template <int NV, bool EMBED>
 __global__ void __launch_bounds__(LN_WARPS * 32) ln_fwd_kernel(const hstd_ln_args p) {
+  HSTD_PDL_PROLOGUE();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * LN_WARPS + warp;
   if (row >= p.M) return;
@@ -110,6 +111,7 @@ __global__ void __launch_bounds__(LN_WARPS * 32) ln_fwd_kernel(const hstd_ln_arg
 // registers -> 8 warps per SM and 1.3 TB/s; the split runs both halves at high occupancy.)
 template <int NV>
 __global__ void __launch_bounds__(LN_WARPS * 32) ln_bwd_rows_kernel(const hstd_ln_bwd_args p) {
+  HSTD_PDL_PROLOGUE();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * LN_WARPS + warp;
   if (row >= p.M) return;
@@ -165,6 +167,7 @@ __global__ void __launch_bounds__(LN_WARPS * 32) ln_bwd_rows_kernel(const hstd_l
 // partials layout: [gridDim.y][3][d] floats (dgamma, dbeta, dbias); grid (d/256, LN_COL_ROWGROUPS)
 constexpr int LN_COL_ROWGROUPS = 96;  // 3 x 96 = 288 blocks at d = 768: two per SM
 __global__ void __launch_bounds__(256) ln_bwd_cols_kernel(const hstd_ln_bwd_args p) {
+  HSTD_PDL_PROLOGUE();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int d = p.d;
   const int col = blockIdx.x * 256 + lane * 8;
@@ -218,6 +221,7 @@ constexpr int FIN_COLS = 32, FIN_GROUPS = 8;
 __global__ void __launch_bounds__(FIN_COLS * FIN_GROUPS)
 partials_finalize_kernel(const float* __restrict__ partials, int nparts, int width, int seg, __nv_bfloat16* d0,
                          __nv_bfloat16* d1, __nv_bfloat16* d2) {
+  HSTD_PDL_PROLOGUE();
   const int lc = threadIdx.x & (FIN_COLS - 1), grp = threadIdx.x / FIN_COLS;
   const int c = blockIdx.x * FIN_COLS + lc;
   float s = 0.f;
@@ -242,6 +246,7 @@ constexpr int COLSUM_ROWGROUPS = 32;       // built-in-scratch entry point (512 
 constexpr int COLSUM_ROWGROUPS_WS = 96;    // caller-workspace entry point: more blocks in flight
 __global__ void __launch_bounds__(256) colsum_partial_kernel(const __nv_bfloat16* __restrict__ x, int64_t ld, int M,
                                                              int N, float* __restrict__ partials) {
+  HSTD_PDL_PROLOGUE();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int col = blockIdx.x * 256 + lane * 8;
   float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -447,8 +452,8 @@ extern "C" HSTD_API int hstd_ln_fwd(const hstd_ln_args* a, void* stream) {
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const int blocks = (a->M + LN_WARPS - 1) / LN_WARPS;
   const bool embed = a->ids != nullptr;
-  HSTD_DISPATCH_NV(a->d / 256, if (embed) ln_fwd_kernel<NV, true><<<blocks, LN_WARPS * 32, 0, s>>>(*a);
-                   else ln_fwd_kernel<NV, false><<<blocks, LN_WARPS * 32, 0, s>>>(*a));
+  HSTD_DISPATCH_NV(a->d / 256, if (embed) launch_pdl(ln_fwd_kernel<NV, true>, dim3(blocks), dim3(LN_WARPS * 32), 0, s, *a);
+                   else launch_pdl(ln_fwd_kernel<NV, false>, dim3(blocks), dim3(LN_WARPS * 32), 0, s, *a));
   return check_launch("ln_fwd");
 }
 
@@ -459,14 +464,14 @@ extern "C" HSTD_API int hstd_ln_bwd(const hstd_ln_bwd_args* a, void* stream) {
   if (!a->partials) return set_error(-1, "ln_bwd: partials scratch is required");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const int blocks = (a->M + LN_WARPS - 1) / LN_WARPS;
-  HSTD_DISPATCH_NV(a->d / 256, ln_bwd_rows_kernel<NV><<<blocks, LN_WARPS * 32, 0, s>>>(*a));
+  HSTD_DISPATCH_NV(a->d / 256, launch_pdl(ln_bwd_rows_kernel<NV>, dim3(blocks), dim3(LN_WARPS * 32), 0, s, *a));
   if (int rc = check_launch("ln_bwd rows")) return rc;
-  ln_bwd_cols_kernel<<<dim3(a->d / 256, LN_COL_ROWGROUPS), 256, 0, s>>>(*a);
+  launch_pdl(ln_bwd_cols_kernel, dim3(a->d / 256, LN_COL_ROWGROUPS), dim3(256), 0, s, *a);
   if (int rc = check_launch("ln_bwd cols")) return rc;
   const int width = 3 * a->d;
-  partials_finalize_kernel<<<(width + FIN_COLS - 1) / FIN_COLS, FIN_COLS * FIN_GROUPS, 0, s>>>(
-      a->partials, LN_COL_ROWGROUPS, width, a->d, static_cast<__nv_bfloat16*>(a->dgamma),
-      static_cast<__nv_bfloat16*>(a->dbeta), static_cast<__nv_bfloat16*>(a->dbias));
+  launch_pdl(partials_finalize_kernel, dim3((width + FIN_COLS - 1) / FIN_COLS), dim3(FIN_COLS * FIN_GROUPS), 0, s,
+             static_cast<const float*>(a->partials), LN_COL_ROWGROUPS, width, a->d, static_cast<__nv_bfloat16*>(a->dgamma),
+             static_cast<__nv_bfloat16*>(a->dbeta), static_cast<__nv_bfloat16*>(a->dbias));
   return check_launch("ln_bwd finalize");
 }
 
@@ -476,10 +481,11 @@ extern "C" HSTD_API int hstd_colsum(const void* x, int64_t ld, int M, int N, voi
   if (N % 8 != 0) return set_error(-1, "colsum: N must be a multiple of 8");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   dim3 grid((N + 255) / 256, COLSUM_ROWGROUPS_WS);
-  colsum_partial_kernel<<<grid, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(x), ld, M, N, partials);
+  launch_pdl(colsum_partial_kernel, grid, dim3(256), 0, s, static_cast<const __nv_bfloat16*>(x), ld, M, N, partials);
   if (int rc = check_launch("colsum")) return rc;
-  partials_finalize_kernel<<<(N + FIN_COLS - 1) / FIN_COLS, FIN_COLS * FIN_GROUPS, 0, s>>>(
-      partials, COLSUM_ROWGROUPS_WS, N, N, static_cast<__nv_bfloat16*>(out), nullptr, nullptr);
+  launch_pdl(partials_finalize_kernel, dim3((N + FIN_COLS - 1) / FIN_COLS), dim3(FIN_COLS * FIN_GROUPS), 0, s,
+             static_cast<const float*>(partials), COLSUM_ROWGROUPS_WS, N, N, static_cast<__nv_bfloat16*>(out),
+             static_cast<__nv_bfloat16*>(nullptr), static_cast<__nv_bfloat16*>(nullptr));
   return check_launch("colsum finalize");
 }
 

@@ -47,6 +47,7 @@ __global__ void __launch_bounds__(256) adamw_flat_kernel(const StepState* __rest
                                                          const __nv_bfloat16* __restrict__ g, float* __restrict__ w,
                                                          float* __restrict__ m, float* __restrict__ v,
                                                          __nv_bfloat16* __restrict__ wb, int64_t n4, float gscale) {
+  HSTD_PDL_PROLOGUE();
   const AdamScalars sc = load_adam_scalars(st);
   for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n4; i += int64_t(gridDim.x) * blockDim.x) {
     const uint2 gu = reinterpret_cast<const uint2*>(g)[i];
@@ -92,7 +93,7 @@ extern "C" HSTD_API int hstd_adamw_flat(const hstd_step_state* st, const void* g
   int blocks = int((n4 + 255) / 256);
   if (blocks > 148 * 16) blocks = 148 * 16;
   if (blocks < 1) blocks = 1;
-  adamw_flat_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      st, static_cast<const __nv_bfloat16*>(grads), master, m, v, static_cast<__nv_bfloat16*>(w_bf16), n4, grad_scale);
+  launch_pdl(adamw_flat_kernel, dim3(blocks), dim3(256), 0, static_cast<cudaStream_t>(stream), st,
+             static_cast<const __nv_bfloat16*>(grads), master, m, v, static_cast<__nv_bfloat16*>(w_bf16), n4, grad_scale);
   return check_launch("adamw_flat");
 }

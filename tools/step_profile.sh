@@ -2,9 +2,10 @@
 # Per-kernel device time of one training step (eager, no graph) — run on the GPU box.
 # Plain run first (must exit 0), then the same command under ncu (B200_PROFILING.md).
 set -e
-CMD="python bench.py --steps 2 --warmup 3 --no_graph ${BENCH_ARGS}"
+export HSTD_BENCH_NO_COOLDOWN=1
+CMD="python bench.py --steps 1 --warmup 3 --no_graph ${BENCH_ARGS}"
 $CMD > gpurun_out/plain.log 2>&1 &&
-ncu --metrics gpu__time_duration.sum --clock-control none -c 2000 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu.log 2>&1
+ncu --metrics gpu__time_duration.sum --clock-control none -s 340 -c 520 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu.log 2>&1
 python - <<'PY'
 import csv, collections, re
 rows = []
