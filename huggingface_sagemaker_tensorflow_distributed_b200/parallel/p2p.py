@@ -252,6 +252,7 @@ class P2PGroup:
         plan.launches += 1
         if not overlap:
             plan.ops.append(lambda args=args: self.launch(args))
+            plan.names.append(f"allreduce+adamw[{MODE_NAMES[mode]}]")
             return
         ev = torch.cuda.Event()
         self._plan_events.append(ev)
@@ -263,6 +264,7 @@ class P2PGroup:
             self.launch(args, cs)
 
         plan.ops.append(op)
+        plan.names.append(f"allreduce+adamw[{MODE_NAMES[mode]}]@comm")
         plan.uses_comm_stream = True
 
     def record_end(self, plan) -> None:
@@ -277,6 +279,7 @@ class P2PGroup:
             torch.cuda.current_stream().wait_event(ev)
 
         plan.ops.append(op)
+        plan.names.append("join(comm)")
         plan.keep_events = self._plan_events
 
     def describe(self) -> Dict:
