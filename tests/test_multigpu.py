@@ -12,9 +12,16 @@ pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
 HERE = os.path.dirname(os.path.abspath(__file__))
 
 
+def _free_port():
+    import socket
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
 def _run(which, n):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr",
-           "127.0.0.1", "--master-port", "29533", os.path.join(HERE, "mgpu_worker.py"), which]
+           "127.0.0.1", "--master-port", str(_free_port()), os.path.join(HERE, "mgpu_worker.py"), which]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + "\n" + r.stderr[-3000:]
     assert "ALL OK" in r.stdout, r.stdout[-3000:]
