@@ -71,7 +71,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   constexpr uint32_t A_BYTES = GemmCfg<BN, MC>::A_BYTES;
   constexpr uint32_t B_BYTES = GemmCfg<BN, MC>::B_BYTES;   // per CTA
   constexpr int BN_LOCAL = BN / MC;                        // B rows staged by this CTA
-  constexpr uint32_t TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;
+  // two accumulator buffers; TMEM allocations are powers of two, so the 192-wide tile sits in 2 x 256 columns
+  constexpr uint32_t ACC_STRIDE = BN == 192 ? 256 : BN;
+  constexpr uint32_t TMEM_COLS = 2 * ACC_STRIDE < 32 ? 32 : 2 * ACC_STRIDE;
   constexpr uint32_t IDESC = make_idesc_bf16(BLOCK_M * MC, BN, A_MN, B_MN);
   constexpr uint16_t PAIR_MASK = (1u << MC) - 1;
 
@@ -213,7 +215,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         const int kb_end = min(num_kb_total, kb_begin + p.kb_per_split);
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc * BN;
+        const uint32_t d_tmem = tmem_base + acc * ACC_STRIDE;
         for (int kb = kb_begin; kb < kb_end; ++kb) {
           HSTD_GTRACE(2 + 4 * (kb - kb_begin) + 1);  // mma: starts waiting for data
           mbar_wait(&full_bar[stage], phase);
@@ -255,7 +257,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     const int ew = warp - 2;             // 0..7
     const int quarter = warp & 3;        // TMEM lane quarter this warp may read
     const int col_half = ew >> 2;        // which half of the BN columns
-    constexpr int COLS_PER_WARP = BN / 2;
+    // 64-column store tiles: the 192-wide tile splits 128 + 64 between the two warps of a lane quarter
+    constexpr int COLS_H0 = BN == 192 ? 128 : BN / 2;
+    const int col_begin = col_half * COLS_H0;
+    const int ncols = col_half ? BN - COLS_H0 : COLS_H0;
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = first_tile; tile < total_tiles; tile += tile_stride) {
@@ -267,11 +272,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       const int tm = tmp * MC + cta_rank;
       const int z0 = z % p.nb0, z1 = z / p.nb0;
       const int row = tm * BLOCK_M + quarter * 32 + lane;
-      const int col_base = tn * BN + col_half * COLS_PER_WARP;
+      const int col_base = tn * BN + col_begin;
 
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
-      const uint32_t t_row = tmem_base + acc * BN + col_half * COLS_PER_WARP + (uint32_t(quarter * 32) << 16);
+      const uint32_t t_row = tmem_base + acc * ACC_STRIDE + col_begin + (uint32_t(quarter * 32) << 16);
       const int64_t zoff = int64_t(z0) * p.c_bs0 + int64_t(z1) * p.c_bs1;
       if constexpr (BN >= 128) {
         if (p.use_tma_store) {
@@ -282,7 +287,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           uint8_t* stage = smem_stage + ew * 4096;
           const int row0 = tm * BLOCK_M + quarter * 32;
 #pragma unroll 1
-          for (int g = 0; g < COLS_PER_WARP; g += 64) {
+          for (int g = 0; g < ncols; g += 64) {
             const int col0 = col_base + g;
             float f[64];
             {
@@ -369,7 +374,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         }
       }
 #pragma unroll 1
-      for (int c = 0; c < COLS_PER_WARP; c += 32) {
+      for (int c = 0; c < ncols; c += 32) {
         uint32_t v[32];
         tmem_ld_32x32(t_row + c, v);
         tmem_ld_wait();
@@ -573,7 +578,7 @@ static int gemm_impl(const hstd_gemm_args* a, int splits, float* workspace, cuda
   if (a->N % 8 != 0) return set_error(-1, "gemm: N must be a multiple of 8");
   const int nb0 = a->nb0 > 0 ? a->nb0 : 1, nb1 = a->nb1 > 0 ? a->nb1 : 1;
   int bn = a->block_n ? a->block_n : pick_block_n(a->M, a->N, nb0 * nb1, splits);
-  if (bn != 64 && bn != 128 && bn != 256) return set_error(-1, "gemm: block_n must be 64, 128 or 256");
+  if (bn != 64 && bn != 128 && bn != 192 && bn != 256) return set_error(-1, "gemm: block_n must be 64, 128, 192 or 256");
 
   CUtensorMap ta, tb;
   int rc;
@@ -586,6 +591,7 @@ static int gemm_impl(const hstd_gemm_args* a, int splits, float* workspace, cuda
   // 64-wide B tile cannot be split between the pair.
   int mc = (a->M > BLOCK_M && bn >= 128) ? 2 : 1;
   if (a->cluster_m == 1) mc = 1;
+  if (bn == 192 && a->b_mn_major) mc = 1;  // half of an MN-major 192-row B tile is not a whole 64-row chunk
   if (!a->b_mn_major)
     rc = get_tmap(&tb, a->B, a->K, a->N, nb0, nb1, a->ldb, a->b_bs0, a->b_bs1, bn / mc);
   else
@@ -632,6 +638,7 @@ static int gemm_impl(const hstd_gemm_args* a, int splits, float* workspace, cuda
   }
   HSTD_GEMM_CASE(64)
   HSTD_GEMM_CASE(128)
+  HSTD_GEMM_CASE(192)
   HSTD_GEMM_CASE(256)
 #undef HSTD_GEMM_CASE
   return set_error(-1, "gemm: unreachable");

@@ -21,6 +21,7 @@ __device__ __forceinline__ float drop_mult(const Dropout& d, uint64_t idx) {
 
 // h[b,j] = act(b1[j] + sum_k W1[j,k] * drop0(x[b*S, k]));  one warp per (b, j)
 __global__ void __launch_bounds__(256) head_dense_fwd_kernel(const hstd_head_args p) {
+  HSTD_PDL_PROLOGUE();
   const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (gw >= p.B * p.d) return;
   const int b = gw / p.d, j = gw - b * p.d;
@@ -48,6 +49,7 @@ __global__ void __launch_bounds__(256) head_dense_fwd_kernel(const hstd_head_arg
 
 // logits, loss, accuracy, dlogits.  Single block; warp w handles samples w, w+nwarps, ...
 __global__ void __launch_bounds__(1024) head_logits_loss_kernel(const hstd_head_args p) {
+  HSTD_PDL_PROLOGUE();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
   const Dropout d1 = make_dropout(p.train ? p.state : nullptr, p.p_drop, p.site1);
   extern __shared__ float sm[];  // [B] loss, [B] correct, [B] valid
@@ -112,6 +114,7 @@ __global__ void __launch_bounds__(1024) head_logits_loss_kernel(const hstd_head_
 
 // thread per hidden column j: dz[b,j] for all b, dW2[c,j] for all c; thread 0.. also db2.
 __global__ void __launch_bounds__(256) head_bwd_dz_kernel(const hstd_head_args p) {
+  HSTD_PDL_PROLOGUE();
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   const Dropout d1 = make_dropout(p.state, p.p_drop, p.site1);
   const __nv_bfloat16* w2 = static_cast<const __nv_bfloat16*>(p.w2);
@@ -138,6 +141,7 @@ __global__ void __launch_bounds__(256) head_bwd_dz_kernel(const hstd_head_args p
 
 // dW1[j,k] = sum_b dz[b,j] * drop0(x[b,k]);  db1[j] = sum_b dz[b,j].  grid (d/256, d)
 __global__ void __launch_bounds__(256) head_bwd_dw1_kernel(const hstd_head_args p) {
+  HSTD_PDL_PROLOGUE();
   const int k = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y;
   if (k >= p.d) return;
   const Dropout d0 = make_dropout(p.state, p.kind == 2 ? p.p_drop : 0.f, p.site0);
@@ -156,6 +160,7 @@ __global__ void __launch_bounds__(256) head_bwd_dw1_kernel(const hstd_head_args 
 // j-groups, combined through smem (the j loop is the long dimension: d sequential loads).
 constexpr int HDX_COLS = 128, HDX_GROUPS = 8;
 __global__ void __launch_bounds__(HDX_COLS * HDX_GROUPS) head_bwd_dx_kernel(const hstd_head_args p) {
+  HSTD_PDL_PROLOGUE();
   const int lc = threadIdx.x % HDX_COLS, grp = threadIdx.x / HDX_COLS;
   const int k = blockIdx.x * HDX_COLS + lc, b = blockIdx.y;
   const __nv_bfloat16* w1 = static_cast<const __nv_bfloat16*>(p.w1);
@@ -185,9 +190,9 @@ extern "C" HSTD_API int hstd_head_fwd(const hstd_head_args* a, void* stream) {
   if (a->B > 2048) return set_error(-1, "head: batch too large");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const int64_t threads = int64_t(a->B) * a->d * 32;
-  head_dense_fwd_kernel<<<unsigned((threads + 255) / 256), 256, 0, s>>>(*a);
+  launch_pdl(head_dense_fwd_kernel, dim3(unsigned((threads + 255) / 256)), dim3(256), 0, s, *a);
   if (int rc = check_launch("head_dense_fwd")) return rc;
-  head_logits_loss_kernel<<<1, 1024, 3 * a->B * sizeof(float), s>>>(*a);
+  launch_pdl(head_logits_loss_kernel, dim3(1), dim3(1024), 3 * a->B * sizeof(float), s, *a);
   return check_launch("head_logits_loss");
 }
 
@@ -197,10 +202,10 @@ extern "C" HSTD_API int hstd_head_bwd(const hstd_head_args* a, void* stream) {
   cudaError_t e = cudaMemsetAsync(a->dx, 0, size_t(a->B) * a->S * a->d * 2, s);
   if (e != cudaSuccess) return set_error(-6, std::string("head_bwd memset: ") + cudaGetErrorString(e));
   const int cols = a->d > a->C ? a->d : a->C;
-  head_bwd_dz_kernel<<<(cols + 255) / 256, 256, 0, s>>>(*a);
+  launch_pdl(head_bwd_dz_kernel, dim3((cols + 255) / 256), dim3(256), 0, s, *a);
   if (int rc = check_launch("head_bwd_dz")) return rc;
-  head_bwd_dw1_kernel<<<dim3((a->d + 255) / 256, a->d), 256, 0, s>>>(*a);
+  launch_pdl(head_bwd_dw1_kernel, dim3((a->d + 255) / 256, a->d), dim3(256), 0, s, *a);
   if (int rc = check_launch("head_bwd_dw1")) return rc;
-  head_bwd_dx_kernel<<<dim3((a->d + HDX_COLS - 1) / HDX_COLS, a->B), HDX_COLS * HDX_GROUPS, 0, s>>>(*a);
+  launch_pdl(head_bwd_dx_kernel, dim3((a->d + HDX_COLS - 1) / HDX_COLS, a->B), dim3(HDX_COLS * HDX_GROUPS), 0, s, *a);
   return check_launch("head_bwd_dx");
 }

@@ -399,6 +399,7 @@ __global__ void __launch_bounds__(256) embed_bwd_kernel(const __nv_bfloat16* __r
                                                         const int32_t* __restrict__ pos_ids,
                                                         __nv_bfloat16* __restrict__ word_grad,
                                                         __nv_bfloat16* __restrict__ pos_grad, int M, int d) {
+  HSTD_PDL_PROLOGUE();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * 8 + warp;
   if (row >= M) return;
@@ -524,9 +525,9 @@ extern "C" HSTD_API int hstd_embed_bwd(const void* de, const int32_t* ids, const
                                        void* pos_grad, int M, int d, void* stream) {
   if (int rc = check_d(d, "embed_bwd")) return rc;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  HSTD_DISPATCH_NV(d / 256, embed_bwd_kernel<NV><<<(M + 7) / 8, 256, 0, s>>>(
-                                static_cast<const __nv_bfloat16*>(de), ids, pos_ids,
-                                static_cast<__nv_bfloat16*>(word_grad), static_cast<__nv_bfloat16*>(pos_grad), M, d));
+  HSTD_DISPATCH_NV(d / 256, launch_pdl(embed_bwd_kernel<NV>, dim3((M + 7) / 8), dim3(256), 0, s,
+                                       static_cast<const __nv_bfloat16*>(de), ids, pos_ids,
+                                       static_cast<__nv_bfloat16*>(word_grad), static_cast<__nv_bfloat16*>(pos_grad), M, d));
   return check_launch("embed_bwd");
 }
 

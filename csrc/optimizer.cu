@@ -18,6 +18,7 @@ __global__ void step_state_init_kernel(StepState* st, uint64_t seed, int64_t ste
 
 __global__ void step_prologue_kernel(StepState* st, float base_lr, int schedule, int64_t total_steps,
                                      int64_t warmup_steps, float beta1, float beta2, float eps, float weight_decay) {
+  HSTD_PDL_PROLOGUE();
   const int64_t s0 = st->step;  // steps already taken = 0-based index of this step
   const int64_t t = s0 + 1;
   double lr = base_lr;
@@ -78,8 +79,8 @@ extern "C" HSTD_API int hstd_step_state_init(hstd_step_state* st, uint64_t seed,
 extern "C" HSTD_API int hstd_step_prologue(hstd_step_state* st, float base_lr, int schedule, int64_t total_steps,
                                            int64_t warmup_steps, float beta1, float beta2, float eps,
                                            float weight_decay, void* stream) {
-  step_prologue_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(st, base_lr, schedule, total_steps, warmup_steps,
-                                                                       beta1, beta2, eps, weight_decay);
+  launch_pdl(step_prologue_kernel, dim3(1), dim3(1), 0, static_cast<cudaStream_t>(stream), st, base_lr, schedule, total_steps,
+             warmup_steps, beta1, beta2, eps, weight_decay);
   return check_launch("step_prologue");
 }
 extern "C" HSTD_API int hstd_metrics_reset(hstd_step_state* st, void* stream) {

@@ -43,7 +43,8 @@ def find_nvcc() -> str:
 
 
 def _sources() -> list[Path]:
-    return sorted(CSRC.glob("*.cu"))
+    # *.cu: sm_100a kernels; *.cpp: the host runtime (tokenizer, bucket manager, batch loader)
+    return sorted(list(CSRC.glob("*.cu")) + list(CSRC.glob("*.cpp")))
 
 
 def _digest(src: Path) -> str:

@@ -12,7 +12,7 @@ Differences from the reference, all deliberate:
   * missing ``SM_*`` variables fall back to ``./output`` / ``./model`` instead of raising
     ``KeyError`` while the parser is built;
   * extra knobs the north star asks for: ``--weight_decay``, ``--lr_schedule``,
-    ``--warmup_steps``, ``--max_seq_length``, ``--no_shard``, ``--dtype``, ``--max_steps``,
+    ``--warmup_steps``, ``--max_seq_length``, ``--data_source``, ``--prefetch``, ``--no_shard``, ``--dtype``, ``--max_steps``,
     dataset sizing for the synthetic IMDB-shaped data, and bucket size for the all-reduce.
 Unknown flags are ignored (``parse_known_args``), as in the reference.
 """
@@ -73,6 +73,8 @@ class TrainConfig:
     log_every: int = 50
     metrics_jsonl: Optional[str] = None
     save_training_state: bool = False  # also write optimizer moments + step (true resume)
+    data_source: str = "ids"  # ids: synthetic token ids | text: synthetic reviews through the native tokenizer
+    prefetch: bool = True  # C++ batch loader thread + pinned ring (GPU runs)
     train_channel: Optional[str] = None  # SM_CHANNEL_TRAIN
     test_channel: Optional[str] = None  # SM_CHANNEL_TEST
     extra: Dict[str, Any] = field(default_factory=dict)
@@ -116,6 +118,8 @@ def build_parser(distributed: bool = True) -> argparse.ArgumentParser:
     p.add_argument("--log_every", type=int, default=50)
     p.add_argument("--metrics_jsonl", type=str, default=None)
     p.add_argument("--save_training_state", type=str2bool, nargs="?", const=True, default=False)
+    p.add_argument("--data_source", type=str, default="ids", choices=["ids", "text"])
+    p.add_argument("--prefetch", type=str2bool, nargs="?", const=True, default=True)
     p.add_argument("--train_channel", type=str, default=env.get("SM_CHANNEL_TRAIN"))
     p.add_argument("--test_channel", type=str, default=env.get("SM_CHANNEL_TEST"))
     return p

@@ -8,7 +8,13 @@ so the default source is a deterministic **synthetic IMDB-shaped** set: 25 000 t
 sequence length, feeding only ``input_ids`` and ``attention_mask``.  A small planted signal
 (label-dependent token frequencies) makes the loss curve meaningful.  When
 ``SM_CHANNEL_TRAIN`` / ``SM_CHANNEL_TEST`` point at pre-tokenised ``.npz``/``.pt`` files or
-``.jsonl`` text plus a loadable tokenizer, those are used instead.
+``.jsonl`` text plus a loadable tokenizer, those are used instead.  ``data_source="text"``
+generates synthetic review *texts* and runs them through the native C++ WordPiece tokenizer
+(csrc/tokenizer.cpp) — the reference's ``dataset.map(tokenize, batched=True)`` stage.
+
+Batching: ``BatchedDataset`` assembles batches in Python; with ``prefetch=True`` a C++ worker
+thread (csrc/batch_loader.cpp) stages them ahead of the training loop into a ring of pinned
+slots, and a slot is recycled only after a CUDA event proves its H2D copies have run.
 
 Sharding: by default rank r takes samples r, r+W, ... (DistributedSampler semantics) so the
 job consumes each example once; ``no_shard=True`` restores the reference behaviour where
@@ -70,6 +76,29 @@ def synthetic_imdb(cfg: EncoderConfig, num_samples: int, seq_len: int, seed: int
     return TokenizedDataset(ids, mask, labels.astype(np.int32), source="synthetic")
 
 
+def synthetic_imdb_text(cfg: EncoderConfig, tokenizer, num_samples: int, seq_len: int, seed: int = 0,
+                        split: str = "train", padding: str = "max_length") -> TokenizedDataset:
+    """Synthetic review texts -> native tokenizer -> dense ``[N, seq_len]`` tables: steps (1)-(5) of
+    the reference pipeline (scripts/train.py:69-83).  ``padding="longest"`` tokenises like the
+    reference's train split and is then densified to ``seq_len`` with the pad id, as
+    ``to_tensor(shape=[None, model_max_length])`` does (scripts/train.py:80-83)."""
+    from .tokenization import synthetic_reviews
+
+    vocab = [tokenizer.convert_ids_to_tokens(i) for i in range(min(tokenizer.vocab_size, 12000))]
+    texts, labels = synthetic_reviews(num_samples, seed, split, vocab)
+    if hasattr(tokenizer, "encode_dense"):
+        ids, mask = tokenizer.encode_dense(texts, max_length=seq_len, padding=padding)
+    else:  # an HF tokenizer (e.g. a local RoBERTa BPE)
+        enc = tokenizer(texts, truncation=True, padding=padding, max_length=seq_len)
+        ids, mask = np.asarray(enc["input_ids"], dtype=np.int32), np.asarray(enc["attention_mask"], dtype=np.int32)
+    ids, mask = _pad_to(ids, seq_len, 0), _pad_to(mask, seq_len, 0)
+    ids = np.where(mask == 1, ids, cfg.pad_token_id).astype(np.int32)
+    if int(ids.max()) >= cfg.vocab_size:
+        raise ValueError(f"tokenizer produced id {int(ids.max())} >= model vocab_size {cfg.vocab_size}")
+    return TokenizedDataset(np.ascontiguousarray(ids), np.ascontiguousarray(mask.astype(np.int32)), labels,
+                            source="synthetic-text")
+
+
 def _pad_to(a: np.ndarray, seq_len: int, value: int) -> np.ndarray:
     if a.shape[1] == seq_len:
         return a
@@ -114,14 +143,16 @@ def load_channel(path: str, cfg: EncoderConfig, seq_len: int, tokenizer=None) ->
 
 
 def try_load_tokenizer(name_or_path: Optional[str]):
-    """The model's tokenizer if its files are available locally; else None (synthetic ids)."""
-    if not name_or_path or not os.path.isdir(name_or_path):
+    """``AutoTokenizer.from_pretrained`` (scripts/train.py:69): the tokenizer files of a local
+    directory when present, otherwise a synthetic WordPiece vocabulary of the model's size served
+    by the native tokenizer.  None only if the native library has not been built."""
+    if not name_or_path:
         return None
     try:
-        from transformers import AutoTokenizer
+        from .tokenization import AutoTokenizer
 
-        return AutoTokenizer.from_pretrained(name_or_path, local_files_only=True)
-    except Exception:  # noqa: BLE001 - no vocab on disk is the common case here
+        return AutoTokenizer.from_pretrained(name_or_path)
+    except Exception:  # noqa: BLE001 - e.g. libhstd_b200.so absent on a source-only checkout
         return None
 
 
@@ -132,8 +163,11 @@ class BatchedDataset:
     kernels and CUDA graphs see one shape."""
 
     def __init__(self, ds: TokenizedDataset, batch_size: int, rank: int = 0, world_size: int = 1,
-                 shard: bool = True, max_batches: int = -1, pin_memory: bool = False):
+                 shard: bool = True, max_batches: int = -1, pin_memory: bool = False, prefetch: bool = False,
+                 num_slots: int = 4):
         self.ds, self.batch_size = ds, int(batch_size)
+        self.prefetch, self.num_slots = bool(prefetch), max(3, int(num_slots))
+        self._loader = None
         idx = np.arange(len(ds))
         if shard and world_size > 1:
             idx = idx[rank::world_size]
@@ -149,7 +183,59 @@ class BatchedDataset:
     def num_samples(self) -> int:
         return min(len(self.indices), len(self) * self.batch_size)
 
+    # ------------------------------------------------------------------ native prefetching path
+    def _ensure_loader(self):
+        if self._loader is not None:
+            return self._loader
+        from .ops.host import NativeLoader
+
+        bs, S = self.batch_size, self.ds.seq_len
+        mk = (lambda *shape: torch.empty(*shape, dtype=torch.int32).pin_memory()) if self.pin_memory else \
+             (lambda *shape: torch.empty(*shape, dtype=torch.int32))
+        self._slots = [(mk(bs, S), mk(bs, S), mk(bs)) for _ in range(self.num_slots)]
+        tables = tuple(np.ascontiguousarray(a, dtype=np.int32) for a in
+                       (self.ds.input_ids, self.ds.attention_mask, self.ds.labels))
+        self._loader = NativeLoader(*tables, self.indices, bs, len(self),
+                                    [tuple(t.data_ptr() for t in slot) for slot in self._slots],
+                                    pad_id=0, ignore_label=IGNORE_LABEL)
+        return self._loader
+
+    def _iter_prefetch(self) -> Iterator[Tuple[Dict[str, torch.Tensor], torch.Tensor]]:
+        """Yields views of the pinned ring.  A batch stays valid until two more batches have been
+        requested; its slot goes back to the worker only after an event recorded behind the
+        consumer's work on that batch has completed, so the host also never runs more than two
+        steps ahead of the device."""
+        ld = self._ensure_loader()
+        ld.start_epoch()
+        cuda = self.pin_memory
+        held: list = []  # [(slot, event-or-None)] oldest first
+        try:
+            while True:
+                if held and cuda and held[-1][1] is None:
+                    ev = torch.cuda.Event()
+                    ev.record()
+                    held[-1] = (held[-1][0], ev)
+                while len(held) >= 2:
+                    slot, ev = held.pop(0)
+                    if ev is not None:
+                        ev.synchronize()
+                    ld.release(slot)
+                slot = ld.next()
+                if slot < 0:
+                    break
+                held.append((slot, None))
+                ids, mask, lab = self._slots[slot]
+                yield {"input_ids": ids, "attention_mask": mask}, lab
+        finally:
+            if cuda:
+                torch.cuda.synchronize()
+            for slot, _ in held:
+                ld.release(slot)
+
     def __iter__(self) -> Iterator[Tuple[Dict[str, torch.Tensor], torch.Tensor]]:
+        if self.prefetch:
+            yield from self._iter_prefetch()
+            return
         bs, S = self.batch_size, self.ds.seq_len
         for b in range(len(self)):
             sel = self.indices[b * bs:(b + 1) * bs]
@@ -171,11 +257,19 @@ class BatchedDataset:
 
 def build_datasets(cfg: EncoderConfig, *, train_samples: int, test_samples: int, seq_len: int, seed: int,
                    train_channel: Optional[str] = None, test_channel: Optional[str] = None,
-                   tokenizer=None) -> Tuple[TokenizedDataset, TokenizedDataset]:
+                   tokenizer=None, data_source: str = "ids") -> Tuple[TokenizedDataset, TokenizedDataset]:
+    """``data_source``: "ids" draws synthetic token ids directly; "text" generates review texts and
+    tokenises them (needs ``tokenizer``).  Channel directories, when given and readable, win."""
     train = load_channel(train_channel, cfg, seq_len, tokenizer) if train_channel else None
     test = load_channel(test_channel, cfg, seq_len, tokenizer) if test_channel else None
+    if data_source == "text" and tokenizer is None:
+        raise ValueError("data_source='text' needs a tokenizer")
     if train is None:
-        train = synthetic_imdb(cfg, train_samples, seq_len, seed, "train")
+        # the reference pads the train split to the longest example and the test split to max_length
+        # before densifying both to model_max_length (scripts/train.py:76,90)
+        train = (synthetic_imdb_text(cfg, tokenizer, train_samples, seq_len, seed, "train", padding="longest")
+                 if data_source == "text" else synthetic_imdb(cfg, train_samples, seq_len, seed, "train"))
     if test is None:
-        test = synthetic_imdb(cfg, test_samples, seq_len, seed, "test")
+        test = (synthetic_imdb_text(cfg, tokenizer, test_samples, seq_len, seed, "test", padding="max_length")
+                if data_source == "text" else synthetic_imdb(cfg, test_samples, seq_len, seed, "test"))
     return train, test

@@ -38,21 +38,21 @@ class Bucket:
         return self.end - self.start
 
 
+HEAD_PARAMS = ("head.out.weight", "head.out.bias", "head.dense.weight", "head.dense.bias")
+
+
 def plan_buckets(slots: Dict[str, "object"], order: List[str], bucket_elems: int, world: int) -> List[Bucket]:
-    """Greedy contiguous bucketing in backward-ready order.  Bucket boundaries fall on
-    parameter boundaries; sizes are padded by the arena alignment so every bucket splits
-    into ``world`` 16-byte-aligned slices."""
-    buckets: List[Bucket] = []
-    cur_names: List[str] = []
-    cur_start = 0
-    for n in order:
-        s = slots[n]
-        if cur_names and (s.end - cur_start) > bucket_elems:
-            buckets.append(Bucket(len(buckets), cur_start, s.offset, cur_names))
-            cur_names, cur_start = [], s.offset
-        cur_names.append(n)
-    if cur_names:
-        buckets.append(Bucket(len(buckets), cur_start, slots[order[-1]].end, cur_names))
+    """Greedy contiguous bucketing in backward-ready order, done by the native bucket manager
+    (csrc/bucket_manager.cpp: hstd_bucket_plan).  Bucket boundaries fall on parameter
+    boundaries; sizes are padded by the arena alignment so every bucket splits into ``world``
+    16-byte-aligned slices."""
+    from ..ops import host
+
+    spans, param_bucket = host.bucket_plan([slots[n].offset for n in order], [slots[n].end for n in order],
+                                           bucket_elems)
+    buckets = [Bucket(i, a, b, []) for i, (a, b) in enumerate(spans)]
+    for n, bi in zip(order, param_bucket):
+        buckets[bi].names.append(n)
     return buckets
 
 
@@ -66,6 +66,13 @@ class DPEngine:
         order = list(engine.slots.keys())
         self.buckets = plan_buckets(engine.slots, order, int(bucket_mb * (1 << 20) / 2), self.world)
         self.name_to_bucket = {n: b.index for b in self.buckets for n in b.names}
+        from ..ops import host
+
+        # readiness bookkeeping lives in the native tracker; head gradients are produced first and
+        # never announced separately, so they are exempt
+        self._param_index = {n: i for i, n in enumerate(order)}
+        self._tracker = host.BucketTracker([self.name_to_bucket[n] for n in order],
+                                           [n in HEAD_PARAMS for n in order], len(self.buckets))
         self.distributed = False
         self._pending_full = None
         self._opt_stream = None
@@ -171,27 +178,14 @@ class DPEngine:
 
     # ------------------------------------------------------------------ hooks used while recording a plan
     def begin_backward(self, plan) -> None:
-        self._pending = set()
-        self._done_buckets = set()
-        self._bucket_left = {b.index: set(b.names) for b in self.buckets}
+        self._tracker.reset()
         if self.p2p is not None and self.distributed:
             self.p2p.record_begin(plan)
 
     def after_grads(self, plan, names: List[str]) -> None:
-        """Called (at record time) once the gradients of ``names`` have been produced."""
-        ready = []
-        for n in names:
-            b = self.name_to_bucket[n]
-            self._bucket_left[b].discard(n)
-        # head gradients are produced first and never announced separately
-        for b in self.buckets:
-            left = self._bucket_left[b.index] - {"head.out.weight", "head.out.bias", "head.dense.weight",
-                                                 "head.dense.bias"}
-            if not left and b.index not in self._done_buckets:
-                # buckets complete strictly in order because the arena is in readiness order
-                if all(i in self._done_buckets for i in range(b.index)):
-                    ready.append(b)
-                    self._done_buckets.add(b.index)
+        """Called (at record time) once the gradients of ``names`` have been produced.  The
+        tracker releases buckets strictly in order because the arena is in readiness order."""
+        ready = [self.buckets[i] for i in self._tracker.mark([self._param_index[n] for n in names])]
         if self.p2p is not None and self.distributed:
             for b in ready:
                 self.p2p.record_bucket(plan, b, self.engine.state, self.master, self.m, self.v,
@@ -223,7 +217,7 @@ class DPEngine:
 
     def end_backward(self, plan) -> None:
         self._pending_full = None  # training is about to start: sharded state is now the truth
-        assert len(self._done_buckets) == len(self.buckets), "every bucket must be complete at end of backward"
+        assert self._tracker.done == len(self.buckets), "every bucket must be complete at end of backward"
         st = self.engine.state
         if self.p2p is not None and self.distributed:
             self.p2p.record_end(plan)

@@ -29,13 +29,14 @@ def build_model_and_data(cfg: TrainConfig, *, rank: int, world: int, per_replica
            {"bucket_mb": cfg.bucket_mb, "comm_mode": cfg.comm, "use_cuda_graph": cfg.cuda_graph}))
     train, test = build_datasets(model.cfg, train_samples=cfg.train_samples, test_samples=cfg.test_samples,
                                  seq_len=seq_len, seed=cfg.seed, train_channel=cfg.train_channel,
-                                 test_channel=cfg.test_channel, tokenizer=model.tokenizer)
+                                 test_channel=cfg.test_channel, tokenizer=model.tokenizer,
+                                 data_source=cfg.data_source)
     pin = model.backend.device.type == "cuda"
     train_ds = BatchedDataset(train, per_replica_train_bs, rank, world, shard=not cfg.no_shard,
-                              max_batches=cfg.max_steps, pin_memory=pin)
+                              max_batches=cfg.max_steps, pin_memory=pin, prefetch=pin and cfg.prefetch)
     # the reference evaluates the full test set on every rank (scripts/train.py:170)
     test_ds = BatchedDataset(test, cfg.eval_batch_size, 0, 1, shard=False, max_batches=cfg.max_eval_steps,
-                             pin_memory=pin)
+                             pin_memory=pin, prefetch=pin and cfg.prefetch)
     return model, train_ds, test_ds
 
 

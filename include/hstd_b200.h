@@ -60,7 +60,7 @@ typedef struct hstd_gemm_args {
   int32_t a_mn_major, b_mn_major;
   int32_t epilogue;
   float alpha;
-  int32_t block_n; /* 0 = auto, else 64/128/256 */
+  int32_t block_n; /* 0 = auto, else 64/128/192/256 */
   int32_t max_ctas; /* 0 = one persistent CTA per SM */
   int32_t cluster_m; /* 0 = auto (2-CTA clusters multicasting B when M > 128), 1 = no clusters */
 } hstd_gemm_args;
@@ -267,6 +267,59 @@ int hstd_ipc_open(const void* handle64, void** ptr);
 int hstd_ipc_close(void* ptr);
 int hstd_ipc_free(void* ptr);
 int hstd_enable_peer_access(int dev, int peer);
+
+/* ------------------------------------------------------------------ host runtime: tokenizer (N6)
+ * Native WordPiece tokenizer: the C++ side of AutoTokenizer.from_pretrained(...)(text,
+ * truncation=True, padding=...) (reference scripts/train.py:69,75-77,89-92).  `vocab_path` is a
+ * BERT vocab.txt (one token per line; [PAD]/[UNK]/[CLS]/[SEP] are looked up by name).
+ * hstd_tok_encode_batch writes dense row-major int32 [n, max_len] ids and masks (rows truncated
+ * to max_len, padded with [PAD]); lengths[r] (optional) is the untruncated token count with the
+ * specials.  num_threads <= 0 picks a default.  None of these touch the GPU. */
+typedef struct hstd_tokenizer hstd_tokenizer;
+hstd_tokenizer* hstd_tok_create(const char* vocab_path, int do_lower_case, int strip_accents);
+void hstd_tok_destroy(hstd_tokenizer* tok);
+int hstd_tok_vocab_size(const hstd_tokenizer* tok);
+int hstd_tok_token_to_id(const hstd_tokenizer* tok, const char* token); /* -1 if absent */
+const char* hstd_tok_id_to_token(const hstd_tokenizer* tok, int id);    /* NULL if out of range */
+int hstd_tok_special_ids(const hstd_tokenizer* tok, int32_t* out4);     /* pad, unk, cls, sep */
+int hstd_tok_encode_batch(const hstd_tokenizer* tok, const char* const* texts, int n, int max_len,
+                          int add_special_tokens, int32_t* ids, int32_t* mask, int32_t* lengths, int num_threads);
+
+/* ------------------------------------------------------------------ host runtime: fusion-bucket manager (N1)
+ * What Horovod's C++ core does with its tensor-fusion buffer (reached from reference
+ * scripts/train.py:114): decide which gradients travel together and notice when a group is
+ * complete.  Parameters are given in arena (= backward-readiness) order by their element offsets;
+ * a bucket is a contiguous range cut at parameter boundaries once it would exceed bucket_elems.
+ *   hstd_bucket_plan: fills starts/ends (capacity max_buckets) and param_bucket[n]; returns the
+ *     number of buckets (negative on error).
+ *   tracker: mark parameters whose gradients now exist; buckets are released strictly in arena
+ *     order, a bucket only after all its non-exempt parameters are marked. */
+int hstd_bucket_plan(const int64_t* offsets, const int64_t* ends, int n, int64_t bucket_elems, int64_t* starts,
+                     int64_t* bucket_ends, int32_t* param_bucket, int max_buckets);
+typedef struct hstd_bucket_tracker hstd_bucket_tracker;
+hstd_bucket_tracker* hstd_bucket_tracker_create(const int32_t* param_bucket, const uint8_t* exempt, int n, int num_buckets);
+void hstd_bucket_tracker_destroy(hstd_bucket_tracker* t);
+void hstd_bucket_tracker_reset(hstd_bucket_tracker* t);
+/* returns how many bucket indices were written to ready_out (capacity = num_buckets) */
+int hstd_bucket_tracker_mark(hstd_bucket_tracker* t, const int32_t* params, int k, int32_t* ready_out);
+int hstd_bucket_tracker_done(const hstd_bucket_tracker* t); /* number of buckets released so far */
+
+/* ------------------------------------------------------------------ host runtime: prefetching batch loader (C11)
+ * tf.data's from_tensor_slices(...).batch(bs) runs in TF's C++ runtime (reference
+ * scripts/train.py:84-86,98-100).  Equivalent here: a worker thread gathers the rows
+ * indices[b*bs .. (b+1)*bs) of the int32 [N,S] id / mask tables and the [N] labels into a ring
+ * of caller-owned (pinned) slots ahead of the consumer.  A short final batch is filled with
+ * pad_id / mask 0 (first position 1) / ignore_label.  next() blocks until the next batch is
+ * staged and returns its slot (or -1 after the last batch); release() hands the slot back. */
+typedef struct hstd_loader hstd_loader;
+hstd_loader* hstd_loader_create(const int32_t* ids, const int32_t* mask, const int32_t* labels, int64_t n_rows,
+                                int seq_len, const int64_t* indices, int64_t n_indices, int batch, int num_batches,
+                                int num_slots, int32_t* const* slot_ids, int32_t* const* slot_mask,
+                                int32_t* const* slot_labels, int32_t pad_id, int32_t ignore_label);
+void hstd_loader_destroy(hstd_loader* l);
+int hstd_loader_start_epoch(hstd_loader* l);
+int hstd_loader_next(hstd_loader* l);
+int hstd_loader_release(hstd_loader* l, int slot);
 
 #ifdef __cplusplus
 }

@@ -21,7 +21,7 @@ def _close(got, want, tol=0.02):
 
 
 @pytest.mark.parametrize("a_t,b_t", [(False, False), (False, True), (True, False), (True, True)])
-@pytest.mark.parametrize("bn", [64, 128, 256])
+@pytest.mark.parametrize("bn", [64, 128, 192, 256])
 @pytest.mark.parametrize("M,N,K", [(128, 256, 64), (384, 768, 192), (200, 328, 136)])
 def test_all_operand_layouts(a_t, b_t, bn, M, N, K):
     from huggingface_sagemaker_tensorflow_distributed_b200.ops import gemm as G
@@ -68,6 +68,31 @@ def test_epilogues_bias_gelu_add_gelubwd():
     uf = u.float().requires_grad_(True)
     torch.nn.functional.gelu(uf).sum().backward()
     _close(G.gemm(X, W, epilogue=G.EPI_GELU_BWD, aux=u), _ref(X, W, False, False) * uf.grad)
+
+
+@pytest.mark.parametrize("cluster_m", [0, 1])
+def test_192_wide_tiles_multi_tile_epilogues_and_split(cluster_m):
+    """BN = 192: 128 tiles for the N = 768 projections (one per SM instead of 96), accumulators
+    at TMEM columns 0 / 256, store tiles split 128 + 64 between the warps of a lane quarter."""
+    from huggingface_sagemaker_tensorflow_distributed_b200.ops import gemm as G
+    torch.manual_seed(5)
+    X, W, b = _mk((4096, 3072), 0.5), _mk((768, 3072), 0.05), _mk((768,))
+    z = _ref(X, W, False, False) + b.float()
+    _close(G.gemm(X, W, bias=b, block_n=192, cluster_m=cluster_m), z)
+    R = _mk((4096, 768))
+    _close(G.gemm(X, W, bias=b, epilogue=G.EPI_ADD, aux=R, block_n=192, cluster_m=cluster_m), z + R.float())
+    pre = torch.empty(4096, 768, dtype=torch.bfloat16, device="cuda")
+    out = G.gemm(X, W, bias=b, epilogue=G.EPI_GELU, aux=pre, block_n=192, cluster_m=cluster_m)
+    _close(pre, z)
+    _close(out, torch.nn.functional.gelu(z))
+    dY, W2 = _mk((4096, 2304), 0.5), _mk((2304, 768), 0.05)
+    _close(G.gemm(dY, W2, b_t=True, block_n=192, cluster_m=cluster_m), _ref(dY, W2, False, True))  # dgrad (MN-major B)
+    Xs = _mk((4096, 768))
+    _close(G.gemm(dY, Xs, a_t=True, b_t=True, block_n=192, cluster_m=cluster_m), _ref(dY, Xs, True, True))  # wgrad
+    _close(G.gemm(dY, Xs, a_t=True, b_t=True, block_n=192, splits=4, cluster_m=cluster_m), _ref(dY, Xs, True, True))
+    # N not a multiple of 192: the last tile column is clipped
+    W3 = _mk((1024, 3072), 0.05)
+    _close(G.gemm(X, W3, block_n=192, cluster_m=cluster_m), _ref(X, W3, False, False))
 
 
 @pytest.mark.parametrize("splits", [2, 4, 7])

@@ -108,4 +108,6 @@ def test_mirrored_strategy_single_command_fans_out_to_replicas(tmp_path):
     assert "[0]" in r.stdout and "[1]" in r.stdout and "replica 1 of 2" in r.stdout
     assert sorted(os.listdir(tmp_path / "out")) == ["eval_results.txt", "train_results.txt"]
     assert "train_runtime" not in open(tmp_path / "out" / "train_results.txt").read()
-    assert sorted(os.listdir(tmp_path / "model")) == ["config.json", "model.safetensors"]
+    # model + tokenizer files, as model.save_pretrained + tokenizer.save_pretrained leave them (scripts/train.py:182-183)
+    assert sorted(os.listdir(tmp_path / "model")) == ["config.json", "model.safetensors", "special_tokens_map.json",
+                                                      "tokenizer_config.json", "vocab.txt"]

@@ -90,7 +90,8 @@ def test_two_rank_gloo_equals_one_rank_with_double_batch(tmp_path):
     sd1 = torch.load(tmp_path / "sd_w2_r1.pt")
     for k in sd0:
         assert torch.equal(sd0[k], sd1[k]), f"ranks diverged on {k}"
-    assert sorted(os.listdir(tmp_path / "w2")) == ["config.json", "model.safetensors"]
+    assert sorted(os.listdir(tmp_path / "w2")) == ["config.json", "model.safetensors", "special_tokens_map.json",
+                                                   "tokenizer_config.json", "vocab.txt"]
     # single process, same init as rank 0, same samples per step in one batch of 8
     model = T.AutoModelForSequenceClassification.from_pretrained("tiny-distilbert", device=torch.device("cpu"),
                                                                 seed=100, dropout=0.0)
