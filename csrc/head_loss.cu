@@ -19,35 +19,54 @@ __device__ __forceinline__ float drop_mult(const Dropout& d, uint64_t idx) {
   return m[idx & 7];
 }
 
-// h[b,j] = act(b1[j] + sum_k W1[j,k] * drop0(x[b*S, k]));  one warp per (b, j)
+constexpr int HB = 8;  // batch rows handled together (weights are read once per HB rows)
+
+// h[b,j] = act(b1[j] + sum_k W1[j,k] * drop0(x[b*S, k]));  one warp per output feature j: the
+// W1 row is read once and used for HB batch rows at a time.
 __global__ void __launch_bounds__(256) head_dense_fwd_kernel(const hstd_head_args p) {
   HSTD_PDL_PROLOGUE();
-  const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (gw >= p.B * p.d) return;
-  const int b = gw / p.d, j = gw - b * p.d;
+  const int j = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (j >= p.d) return;
   const Dropout d0 = make_dropout(p.train ? p.state : nullptr, p.kind == 2 ? p.p_drop : 0.f, p.site0);
-  const __nv_bfloat16* x = static_cast<const __nv_bfloat16*>(p.x) + int64_t(b) * p.S * p.d;
+  const __nv_bfloat16* x = static_cast<const __nv_bfloat16*>(p.x);
   const __nv_bfloat16* w = static_cast<const __nv_bfloat16*>(p.w1) + int64_t(j) * p.d;
-  float acc = 0.f;
-  for (int k = lane * 8; k < p.d; k += 256) {
-    float xv[8], wv[8];
-    load8(x + k, xv);
-    load8(w + k, wv);
-    if (d0.active()) {
-      float m[8];
-      dropout_mask8(d0, (uint64_t(b) * p.d + k) >> 3, m);
+  const float bias = __bfloat162float(static_cast<const __nv_bfloat16*>(p.b1)[j]);
+  for (int b0 = 0; b0 < p.B; b0 += HB) {
+    float acc[HB];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) xv[i] *= m[i];
+    for (int bb = 0; bb < HB; ++bb) acc[bb] = 0.f;
+    for (int k = lane * 8; k < p.d; k += 256) {
+      float wv[8];
+      load8(w + k, wv);
+#pragma unroll
+      for (int bb = 0; bb < HB; ++bb) {
+        const int b = b0 + bb;
+        if (b < p.B) {
+          float xv[8];
+          load8(x + int64_t(b) * p.S * p.d + k, xv);
+          if (d0.active()) {
+            float m[8];
+            dropout_mask8(d0, (uint64_t(b) * p.d + k) >> 3, m);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) xv[i] *= m[i];
+          }
+#pragma unroll
+          for (int i = 0; i < 8; ++i) acc[bb] += xv[i] * wv[i];
+        }
+      }
     }
 #pragma unroll
-    for (int i = 0; i < 8; ++i) acc += xv[i] * wv[i];
+    for (int bb = 0; bb < HB; ++bb) {
+      const float v = warp_sum(acc[bb]);
+      if (lane == 0 && b0 + bb < p.B) p.h[int64_t(b0 + bb) * p.d + j] = head_act(p.kind, v + bias);
+    }
   }
-  acc = warp_sum(acc);
-  if (lane == 0)
-    p.h[gw] = head_act(p.kind, acc + __bfloat162float(static_cast<const __nv_bfloat16*>(p.b1)[j]));
 }
 
 // logits, loss, accuracy, dlogits.  Single block; warp w handles samples w, w+nwarps, ...
+// In training the dropout of the hidden activation is applied here once, eight elements per
+// Philox call: h is overwritten with the dropped activation hd = h*m and, when a dz buffer is
+// given, dz receives m * act'(h) — head_bwd reads both instead of regenerating the masks.
 __global__ void __launch_bounds__(1024) head_logits_loss_kernel(const hstd_head_args p) {
   HSTD_PDL_PROLOGUE();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
@@ -59,12 +78,51 @@ __global__ void __launch_bounds__(1024) head_logits_loss_kernel(const hstd_head_
   const __nv_bfloat16* w2 = static_cast<const __nv_bfloat16*>(p.w2);
   const __nv_bfloat16* b2 = static_cast<const __nv_bfloat16*>(p.b2);
   for (int b = warp; b < p.B; b += nwarps) {
-    for (int c = 0; c < p.C; ++c) {
-      float acc = 0.f;
-      for (int j = lane; j < p.d; j += 32)
-        acc += p.h[b * p.d + j] * drop_mult(d1, uint64_t(b) * p.d + j) * __bfloat162float(w2[int64_t(c) * p.d + j]);
-      acc = warp_sum(acc);
-      if (lane == 0) p.logits[b * p.C + c] = acc + __bfloat162float(b2[c]);
+    float* hrow = p.h + int64_t(b) * p.d;
+    for (int c0 = 0; c0 < p.C; c0 += 4) {
+      float acc[4] = {0.f, 0.f, 0.f, 0.f};
+      for (int j = lane * 8; j < p.d; j += 256) {
+        float hv[8];
+        *reinterpret_cast<float4*>(&hv[0]) = *reinterpret_cast<const float4*>(hrow + j);
+        *reinterpret_cast<float4*>(&hv[4]) = *reinterpret_cast<const float4*>(hrow + j + 4);
+        if (c0 == 0 && p.train) {
+          float m[8];
+          if (d1.active()) {
+            dropout_mask8(d1, (uint64_t(b) * p.d + j) >> 3, m);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) m[i] = 1.f;
+          }
+          if (p.dz != nullptr) {
+            float g[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) g[i] = m[i] * head_act_grad(p.kind, hv[i]);
+            *reinterpret_cast<float4*>(p.dz + int64_t(b) * p.d + j) = *reinterpret_cast<float4*>(&g[0]);
+            *reinterpret_cast<float4*>(p.dz + int64_t(b) * p.d + j + 4) = *reinterpret_cast<float4*>(&g[4]);
+          }
+          if (d1.active()) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) hv[i] *= m[i];
+            *reinterpret_cast<float4*>(hrow + j) = *reinterpret_cast<float4*>(&hv[0]);
+            *reinterpret_cast<float4*>(hrow + j + 4) = *reinterpret_cast<float4*>(&hv[4]);
+          }
+        }
+#pragma unroll
+        for (int cc = 0; cc < 4; ++cc) {
+          if (c0 + cc < p.C) {
+            float wv[8];
+            load8(w2 + int64_t(c0 + cc) * p.d + j, wv);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) acc[cc] += hv[i] * wv[i];
+          }
+        }
+      }
+#pragma unroll
+      for (int cc = 0; cc < 4; ++cc) {
+        const float v = warp_sum(acc[cc]);
+        if (lane == 0 && c0 + cc < p.C) p.logits[b * p.C + c0 + cc] = v + __bfloat162float(b2[c0 + cc]);
+      }
+      __syncwarp();  // a second pass over the classes re-reads the dropped activations written above
     }
     __syncwarp();
     if (lane == 0) {
@@ -112,24 +170,22 @@ __global__ void __launch_bounds__(1024) head_logits_loss_kernel(const hstd_head_
   }
 }
 
-// thread per hidden column j: dz[b,j] for all b, dW2[c,j] for all c; thread 0.. also db2.
+// thread per hidden column j: dW2[c,j] for all c and dz[b,j] for all b; the first C threads also
+// write db2.  Reads what the forward left behind: h = dropped activation, dz = m * act'(h).
 __global__ void __launch_bounds__(256) head_bwd_dz_kernel(const hstd_head_args p) {
   HSTD_PDL_PROLOGUE();
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
-  const Dropout d1 = make_dropout(p.state, p.p_drop, p.site1);
   const __nv_bfloat16* w2 = static_cast<const __nv_bfloat16*>(p.w2);
   if (j < p.d) {
     for (int c = 0; c < p.C; ++c) {
       float acc = 0.f;
-      for (int b = 0; b < p.B; ++b)
-        acc += p.dlogits[b * p.C + c] * p.h[b * p.d + j] * drop_mult(d1, uint64_t(b) * p.d + j);
+      for (int b = 0; b < p.B; ++b) acc += p.dlogits[b * p.C + c] * p.h[int64_t(b) * p.d + j];
       static_cast<__nv_bfloat16*>(p.dw2)[int64_t(c) * p.d + j] = __float2bfloat16_rn(acc);
     }
     for (int b = 0; b < p.B; ++b) {
       float dh = 0.f;
       for (int c = 0; c < p.C; ++c) dh += p.dlogits[b * p.C + c] * __bfloat162float(w2[int64_t(c) * p.d + j]);
-      const float h = p.h[b * p.d + j];
-      p.dz[b * p.d + j] = dh * drop_mult(d1, uint64_t(b) * p.d + j) * head_act_grad(p.kind, h);
+      p.dz[int64_t(b) * p.d + j] *= dh;
     }
   }
   if (j < p.C) {
@@ -139,45 +195,76 @@ __global__ void __launch_bounds__(256) head_bwd_dz_kernel(const hstd_head_args p
   }
 }
 
-// dW1[j,k] = sum_b dz[b,j] * drop0(x[b,k]);  db1[j] = sum_b dz[b,j].  grid (d/256, d)
+// dW1[j,k] = sum_b dz[b,j] * drop0(x[b,k]);  db1[j] = sum_b dz[b,j].  One thread per (j, 8
+// consecutive k): 16-byte loads of x and one 16-byte store.
 __global__ void __launch_bounds__(256) head_bwd_dw1_kernel(const hstd_head_args p) {
   HSTD_PDL_PROLOGUE();
-  const int k = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y;
-  if (k >= p.d) return;
+  const int kchunks = p.d >> 3;
+  const int item = blockIdx.x * blockDim.x + threadIdx.x;
+  if (item >= p.d * kchunks) return;
+  const int j = item / kchunks, k = (item - j * kchunks) * 8;
   const Dropout d0 = make_dropout(p.state, p.kind == 2 ? p.p_drop : 0.f, p.site0);
   const __nv_bfloat16* x = static_cast<const __nv_bfloat16*>(p.x);
-  float acc = 0.f, accb = 0.f;
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  float accb = 0.f;
   for (int b = 0; b < p.B; ++b) {
-    const float dz = p.dz[b * p.d + j];
-    acc += dz * __bfloat162float(x[int64_t(b) * p.S * p.d + k]) * drop_mult(d0, uint64_t(b) * p.d + k);
+    const float dz = p.dz[int64_t(b) * p.d + j];
+    float xv[8];
+    load8(x + int64_t(b) * p.S * p.d + k, xv);
+    if (d0.active()) {
+      float m[8];
+      dropout_mask8(d0, (uint64_t(b) * p.d + k) >> 3, m);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) xv[i] *= m[i];
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] += dz * xv[i];
     accb += dz;
   }
-  static_cast<__nv_bfloat16*>(p.dw1)[int64_t(j) * p.d + k] = __float2bfloat16_rn(acc);
+  store8(static_cast<__nv_bfloat16*>(p.dw1) + int64_t(j) * p.d + k, acc);
   if (k == 0) static_cast<__nv_bfloat16*>(p.db1)[j] = __float2bfloat16_rn(accb);
 }
 
-// dx[b*S, k] = drop0'( sum_j dz[b,j] * W1[j,k] ).  grid (d/128, B); block = 128 columns x 8
-// j-groups, combined through smem (the j loop is the long dimension: d sequential loads).
-constexpr int HDX_COLS = 128, HDX_GROUPS = 8;
+// dx[b*S, k] = drop0'( sum_j dz[b,j] * W1[j,k] ).  grid (d/64, ceil(B/8)); block = 64 columns x 8
+// j-groups.  dz of the HB batch rows is staged in smem so every W1 element is read once per HB
+// rows; the j-groups are combined through the same smem afterwards.
+constexpr int HDX_COLS = 64, HDX_GROUPS = 8, HDX_MAX_D = 1024;
+static_assert(HDX_GROUPS == HB, "the final stage maps j-group g to batch row b0 + g");
 __global__ void __launch_bounds__(HDX_COLS * HDX_GROUPS) head_bwd_dx_kernel(const hstd_head_args p) {
   HSTD_PDL_PROLOGUE();
+  __shared__ float sh[HB * HDX_MAX_D];  // dz[HB][d], then red[HDX_GROUPS][HB][HDX_COLS] (16 KiB of it)
   const int lc = threadIdx.x % HDX_COLS, grp = threadIdx.x / HDX_COLS;
-  const int k = blockIdx.x * HDX_COLS + lc, b = blockIdx.y;
+  const int k = blockIdx.x * HDX_COLS + lc, b0 = blockIdx.y * HB;
+  for (int i = threadIdx.x; i < HB * p.d; i += blockDim.x) {
+    const int bb = i / p.d, j = i - bb * p.d;
+    sh[i] = (b0 + bb < p.B) ? p.dz[int64_t(b0 + bb) * p.d + j] : 0.f;
+  }
+  __syncthreads();
   const __nv_bfloat16* w1 = static_cast<const __nv_bfloat16*>(p.w1);
-  float acc = 0.f;
+  float acc[HB];
+#pragma unroll
+  for (int bb = 0; bb < HB; ++bb) acc[bb] = 0.f;
   if (k < p.d) {
 #pragma unroll 4
-    for (int j = grp; j < p.d; j += HDX_GROUPS) acc += p.dz[b * p.d + j] * __bfloat162float(w1[int64_t(j) * p.d + k]);
-  }
-  __shared__ float red[HDX_GROUPS][HDX_COLS];
-  red[grp][lc] = acc;
-  __syncthreads();
-  if (grp == 0 && k < p.d) {
+    for (int j = grp; j < p.d; j += HDX_GROUPS) {
+      const float w = __bfloat162float(w1[int64_t(j) * p.d + k]);
 #pragma unroll
-    for (int g = 1; g < HDX_GROUPS; ++g) acc += red[g][lc];
+      for (int bb = 0; bb < HB; ++bb) acc[bb] += sh[bb * p.d + j] * w;
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int bb = 0; bb < HB; ++bb) sh[(grp * HB + bb) * HDX_COLS + lc] = acc[bb];
+  __syncthreads();
+  // thread (grp, lc) finishes batch row b0 + grp of column k
+  if (k < p.d && b0 + grp < p.B) {
+    float v = 0.f;
+#pragma unroll
+    for (int g = 0; g < HDX_GROUPS; ++g) v += sh[(g * HB + grp) * HDX_COLS + lc];
+    const int b = b0 + grp;
     const Dropout d0 = make_dropout(p.state, p.kind == 2 ? p.p_drop : 0.f, p.site0);
-    acc *= drop_mult(d0, uint64_t(b) * p.d + k);
-    static_cast<__nv_bfloat16*>(p.dx)[int64_t(b) * p.S * p.d + k] = __float2bfloat16_rn(acc);
+    v *= drop_mult(d0, uint64_t(b) * p.d + k);
+    static_cast<__nv_bfloat16*>(p.dx)[int64_t(b) * p.S * p.d + k] = __float2bfloat16_rn(v);
   }
 }
 
@@ -189,7 +276,8 @@ extern "C" HSTD_API int hstd_head_fwd(const hstd_head_args* a, void* stream) {
   if (a->d % 8 != 0) return set_error(-1, "head: d must be a multiple of 8");
   if (a->B > 2048) return set_error(-1, "head: batch too large");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  const int64_t threads = int64_t(a->B) * a->d * 32;
+  if (a->d > HDX_MAX_D) return set_error(-1, "head: d must be <= 1024");
+  const int64_t threads = int64_t(a->d) * 32;
   launch_pdl(head_dense_fwd_kernel, dim3(unsigned((threads + 255) / 256)), dim3(256), 0, s, *a);
   if (int rc = check_launch("head_dense_fwd")) return rc;
   launch_pdl(head_logits_loss_kernel, dim3(1), dim3(1024), 3 * a->B * sizeof(float), s, *a);
@@ -204,8 +292,9 @@ extern "C" HSTD_API int hstd_head_bwd(const hstd_head_args* a, void* stream) {
   const int cols = a->d > a->C ? a->d : a->C;
   launch_pdl(head_bwd_dz_kernel, dim3((cols + 255) / 256), dim3(256), 0, s, *a);
   if (int rc = check_launch("head_bwd_dz")) return rc;
-  launch_pdl(head_bwd_dw1_kernel, dim3((a->d + 255) / 256, a->d), dim3(256), 0, s, *a);
+  launch_pdl(head_bwd_dw1_kernel, dim3(unsigned((int64_t(a->d) * (a->d / 8) + 255) / 256)), dim3(256), 0, s, *a);
   if (int rc = check_launch("head_bwd_dw1")) return rc;
-  launch_pdl(head_bwd_dx_kernel, dim3((a->d + HDX_COLS - 1) / HDX_COLS, a->B), dim3(HDX_COLS * HDX_GROUPS), 0, s, *a);
+  launch_pdl(head_bwd_dx_kernel, dim3((a->d + HDX_COLS - 1) / HDX_COLS, (a->B + HB - 1) / HB), dim3(HDX_COLS * HDX_GROUPS), 0, s,
+             *a);
   return check_launch("head_bwd_dx");
 }

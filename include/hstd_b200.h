@@ -210,10 +210,12 @@ int hstd_embed_bwd(const void* de, const int32_t* ids, const int32_t* pos_ids, v
  * (drop-Linear-tanh-drop-Linear).  labels int32 [B], -1 = ignore.  Loss is the mean over valid
  * rows of sparse softmax cross-entropy from logits (reference scripts/train.py:118-119).
  * forward writes logits [B,C] fp32, dlogits (d loss / d logits, already divided by the valid
- * count), h [B,d] fp32 (post-activation, pre-dropout), sets state->metrics =
- * {loss_sum, correct, count} and adds them to state->metrics_acc.  `train` != 0 enables dropout.
- * backward (train only) writes dW1,db1,dW2,db2 (bf16) and the CLS rows of dx (bf16 [B*S,d],
- * other rows are zeroed here). */
+ * count), h [B,d] fp32 (post-activation; with `train` != 0 already multiplied by the dropout
+ * mask), sets state->metrics = {loss_sum, correct, count} and adds them to state->metrics_acc.
+ * `train` != 0 enables dropout and, when dz is given, leaves mask * act'(h) in dz [B,d] fp32.
+ * backward (train only; must follow a forward with train != 0 on the same h / dz buffers, which
+ * carry the dropout mask so it is not regenerated) writes dW1,db1,dW2,db2 (bf16), dz, and the CLS
+ * rows of dx (bf16 [B*S,d], other rows are zeroed here).  d <= 1024. */
 typedef struct hstd_head_args {
   const void* x; const void* w1; const void* b1; const void* w2; const void* b2;
   const int32_t* labels;

@@ -202,6 +202,57 @@ def test_head_loss_fwd_bwd(kind):
     assert (dx.view(B, S, d)[:, 1:] == 0).all()
 
 
+@pytest.mark.parametrize("kind", ["distilbert", "bert"])
+def test_head_dropout_mask_is_shared_between_forward_and_backward(kind):
+    """Dropout on the hidden activation: the forward leaves h*m in h, so the mask can be read
+    back (m = 0 or 1/keep) and every output checked against autograd with that same mask."""
+    k = K()
+    torch.manual_seed(1)
+    B, S, d, C, p = 8, 4, 768, 3, 0.2
+    x = bf(B * S, d)
+    w1, b1, w2, b2 = bf(d, d, scale=0.05), bf(d, scale=0.1), bf(C, d, scale=0.2), bf(C, scale=0.1)
+    labels = torch.tensor([0, 1, 2, 0, 2, 1, -1, 1], dtype=torch.int32, device="cuda")
+    st = k.new_step_state("cuda", seed=9)
+    logits, dlogits = torch.empty(B, C, device="cuda"), torch.empty(B, C, device="cuda")
+    h, dz = torch.empty(B, d, device="cuda"), torch.empty(B, d, device="cuda")
+    dw1, db1, dw2, db2 = torch.empty_like(w1), torch.empty_like(b1), torch.empty_like(w2), torch.empty_like(b2)
+    dx = torch.empty((B * S, d), dtype=torch.bfloat16, device="cuda")
+    args = k.make_head_args(x=x, w1=w1, b1=b1, w2=w2, b2=b2, labels=labels, logits=logits, dlogits=dlogits, h=h, dz=dz,
+                            state=st, B=B, S=S, d=d, num_labels=C, kind=kind, p_drop=p, site0=1, site1=2, dw1=dw1,
+                            db1=db1, dw2=dw2, db2=db2, dx=dx)
+    k.head_fwd(args, train=True)
+    hd = h.clone()
+    k.head_bwd(args)
+    xc = x.view(B, S, d)[:, 0].float().requires_grad_(True)
+    W1, B1, W2, B2 = (t.float().requires_grad_(True) for t in (w1, b1, w2, b2))
+    z = xc @ W1.t() + B1
+    hh = torch.relu(z) if kind == "distilbert" else torch.tanh(z)
+    keep_q = 1.0 - round(p * 256) / 256.0
+    big = hh.detach().abs() > 1e-3
+    m = torch.where(hd.abs() > 0, torch.full_like(hd, 1.0 / keep_q), torch.zeros_like(hd))
+    # where the activation is clearly non-zero the stored value is exactly h/keep or 0
+    ratio = (hd / hh.detach())[big]
+    assert ((ratio.abs() < 1e-6) | ((ratio - 1.0 / keep_q).abs() < 2e-2)).all()
+    drop_rate = 1.0 - (ratio.abs() > 1e-6).float().mean().item()
+    assert abs(drop_rate - (1.0 - keep_q)) < 0.03
+    m = torch.where(big, m, torch.full_like(m, 1.0 / keep_q))  # relu zeros: the mask is unobservable and irrelevant
+    lg = (hh * m) @ W2.t() + B2
+    valid = labels >= 0
+    (F.cross_entropy(lg[valid], labels[valid].long(), reduction="sum") / valid.sum()).backward()
+    if kind == "distilbert":
+        close(logits, lg, 2e-3, 2e-3)
+        close(dw2, W2.grad, 2e-3, 2e-2)
+        close(dw1, W1.grad, 2e-3, 3e-2)
+        close(db1, B1.grad, 2e-3, 2e-2)
+        close(dx.view(B, S, d)[:, 0], xc.grad, 2e-3, 2e-2)
+    else:  # tanh: tiny activations were given mask 1/keep above, so allow for the few that were dropped
+        close(logits, lg, 5e-3, 5e-3)
+        close(dw2, W2.grad, 5e-3, 5e-2)
+    # a second forward + backward of the same step regenerates the same mask
+    k.head_fwd(args, train=True)
+    assert torch.equal(h, hd)
+
+
 def test_adamw_flat_matches_keras_formula_and_prologue_schedule():
     k = K()
     from huggingface_sagemaker_tensorflow_distributed_b200.optim import KerasAdamW, LRSchedule
