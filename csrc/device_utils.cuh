@@ -57,6 +57,65 @@ __device__ __forceinline__ void dropout_mask16(const Dropout& d, uint64_t group1
 #pragma unroll
     for (int b = 0; b < 4; ++b) m[4 * i + b] = (((w[i] >> (8 * b)) & 0xFFu) >= d.thresh8) ? d.scale : 0.f;
 }
+// The raw sixteen bytes behind dropout_mask16 (byte b of word i belongs to element 4*i + b), for
+// kernels that apply the mask with bit operations instead of float multipliers.
+__device__ __forceinline__ uint4 dropout_bytes16(const Dropout& d, uint64_t group16) {
+  return philox4x32_7(make_uint4(uint32_t(group16), uint32_t(group16 >> 32), d.site, d.step), d.key);
+}
+// Byte-parallel "byte >= thresh8": x >= t  <=>  x + (256 - t) carries out of the byte.  The low
+// seven bits are added without crossing bytes; the carry out of bit 7 is the majority of the two
+// top bits and the carry into them.  Result: the MSB of every byte is the keep flag (3 instructions
+// for 4 elements; the other bits are garbage).  Needs 1 <= thresh8 <= 255.
+struct KeepConst {
+  uint32_t k4, k7;
+};
+__device__ __forceinline__ KeepConst make_keep_const(const Dropout& d) {
+  KeepConst kc;
+  kc.k4 = (256u - d.thresh8) * 0x01010101u;
+  kc.k7 = kc.k4 & 0x7f7f7f7fu;
+  return kc;
+}
+__device__ __forceinline__ uint32_t keep_flags4(uint32_t x, const KeepConst& kc) {
+  const uint32_t s = (x & 0x7f7f7f7fu) + kc.k7;
+  uint32_t r;
+  asm("lop3.b32 %0, %1, %2, %3, 0xE8;" : "=r"(r) : "r"(x), "r"(kc.k4), "r"(s));  // bitwise majority
+  return r;
+}
+// prmt with sign-replicating selectors: expands flag bytes (MSB = flag) to all-ones / all-zeros lanes
+template <uint32_t SEL>
+__device__ __forceinline__ uint32_t prmt_sel(uint32_t a) {
+  uint32_t r;
+  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(0u), "n"(SEL));
+  return r;
+}
+
+// ------------------------------------------------------------------ packed fp32x2 arithmetic (sm_100)
+// FFMA2 / FADD2 / FMUL2 process two floats per issue slot; the softmax loops of the attention
+// kernels are issue-bound, so this is where their time goes.
+__device__ __forceinline__ uint64_t pack2(float a, float b) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+  return r;
+}
+__device__ __forceinline__ void unpack2(uint64_t v, float& a, float& b) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+}
+__device__ __forceinline__ uint64_t ffma2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ uint64_t fadd2(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ uint64_t fmul2(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+
 // Same stream, addressed in groups of 8 elements (group = element index / 8).
 __device__ __forceinline__ void dropout_mask8(const Dropout& d, uint64_t group, float (&m)[8]) {
   const uint64_t g16 = group >> 1;
