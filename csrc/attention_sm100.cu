@@ -433,7 +433,8 @@ template <int NQ>
 __global__ void __launch_bounds__(AT_THREADS, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
                 const __grid_constant__ CUtensorMap tm_v, const __grid_constant__ CUtensorMap tm_do,
-                const AttnParams p) {
+                const __grid_constant__ CUtensorMap tm_dqp, const __grid_constant__ CUtensorMap tm_dk,
+                const __grid_constant__ CUtensorMap tm_dv, const AttnParams p) {
   HSTD_PDL_PROLOGUE();
   constexpr uint32_t TMEM_COLS = 512;
   constexpr uint32_t C_S = 0, C_DP = 128, C_DV = 256, C_DK = 320, C_DQ = 384;
@@ -448,15 +449,17 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
   uint8_t* sDO = sQ + 2 * TILE_BYTES;   // 2 buffers
   uint8_t* sPd = sDO + 2 * TILE_BYTES;  // 32 KiB
   uint8_t* sDS = sPd + P_BYTES;         // 32 KiB
-  uint32_t* sBits = reinterpret_cast<uint32_t*>(sDS + P_BYTES);  // [4]
+  uint8_t* sDQ = sDS + P_BYTES;         // 2 x 16 KiB staging of the dQ partial for its TMA store
+  uint32_t* sBits = reinterpret_cast<uint32_t*>(sDQ + 2 * TILE_BYTES);  // [4]
   uint64_t* bars = reinterpret_cast<uint64_t*>(sBits + 4);
   uint64_t* bar_kv = bars;
   uint64_t* bar_q = bars + 1;       // [2]
   uint64_t* bar_sdp = bars + 3;
   uint64_t* bar_pds = bars + 4;
   uint64_t* bar_dq = bars + 5;
-  uint64_t* bar_dqread = bars + 6;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 7);
+  uint64_t* bar_dqread = bars + 6;  // dQ of this iteration has left TMEM and sits in its staging tile
+  uint64_t* bar_out = bars + 7;     // dK / dV staged in smem
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int kt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
@@ -485,6 +488,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
       tma_prefetch_desc(&tm_q); tma_prefetch_desc(&tm_k); tma_prefetch_desc(&tm_v); tma_prefetch_desc(&tm_do);
       mbar_init(bar_kv, 1); mbar_init(&bar_q[0], 1); mbar_init(&bar_q[1], 1);
       mbar_init(bar_sdp, 1); mbar_init(bar_pds, AT_ST); mbar_init(bar_dq, 1); mbar_init(bar_dqread, AT_ST);
+      mbar_init(bar_out, AT_ST);
+      tma_prefetch_desc(&tm_dqp); tma_prefetch_desc(&tm_dk); tma_prefetch_desc(&tm_dv);
       fence_mbar_init();
     }
     __syncwarp();
@@ -528,12 +533,16 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
 #pragma unroll
         for (int k = 0; k < DH / 16; ++k) umma_bf16(tmem + C_DP, dDO_k0 + boff + k * 2, dV_k + k * 2, IDESC_S, k > 0);
         umma_commit(bar_sdp);
-        mbar_wait(bar_pds, i & 1);
-        tc_fence_after();
         if (i > 0) {
+          // dQ partial of the previous query tile: staged by the softmax warps, stored by TMA from here
           mbar_wait(bar_dqread, (i - 1) & 1);
           tc_fence_after();
+          tma_store_4d(&tm_dqp, sDQ + ((i - 1) & 1) * TILE_BYTES, h * DH, (i - 1) * TILE, b, kt);
+          tma_store_commit();
+          tma_store_wait_read_le1();  // the store of tile i-2 has read its staging buffer: tile i may overwrite it
         }
+        mbar_wait(bar_pds, i & 1);
+        tc_fence_after();
         // reduction over the 128 query rows of this tile: 8 k-steps of 16 rows = 2048 B each
 #pragma unroll
         for (int k = 0; k < TILE / 16; ++k)
@@ -553,6 +562,15 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
           tma_load_4d(sDO + buf * TILE_BYTES, &tm_do, &bar_q[buf], 0, (i + 2) * TILE, h, b);
         }
       }
+      mbar_wait(bar_dqread, (NQ - 1) & 1);
+      tma_store_4d(&tm_dqp, sDQ + ((NQ - 1) & 1) * TILE_BYTES, h * DH, (NQ - 1) * TILE, b, kt);
+      tma_store_commit();
+      // dK / dV of this key tile: staged by the softmax warps in the (now idle) Pd / dS tiles
+      mbar_wait(bar_out, 0);
+      tma_store_4d(&tm_dk, sDS, 0, kt * TILE, h, b);
+      tma_store_4d(&tm_dv, sPd, 0, kt * TILE, h, b);
+      tma_store_commit();
+      tma_store_wait_read();  // smem is released at CTA exit
     }
   } else {
     const int quarter = warp & 3, half = warp >> 2;
@@ -666,30 +684,45 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
       tc_fence_before();
       fence_proxy_async_smem();
       mbar_arrive(bar_pds);
-      // dQ partial of this (query tile, key tile): this thread stores 32 of the 64 columns
+      // dQ partial of this (query tile, key tile): 32 of the 64 columns per thread, into the swizzled
+      // staging tile; the control thread stores it with one TMA bulk store (per-thread row stores
+      // touched 32 different lines per instruction and cost ~900 cycles per query tile)
       mbar_wait(bar_dq, i & 1);
       tc_fence_after();
       {
         uint32_t v[32];
         tmem_ld_32x32(t_row + C_DQ + half * 32, v);
         tmem_ld_wait();
-        store_out32(p.dq_part + (int64_t(kt) * p.B * S + int64_t(b) * S + i * TILE + row) * d + h * DH + half * 32, v,
-                    p.scale * ik);
+        float f[32];
+        const float sc = p.scale * ik;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * sc;
+        store_row32(sDQ + (i & 1) * TILE_BYTES, row, half * 32, f);
       }
       tc_fence_before();
+      fence_proxy_async_smem();
       mbar_arrive(bar_dqread);
     }
-    // dK (x scale) and dV of this key tile (TMEM lane = key row); the last bar_dq wait covered all MMAs
-    __nv_bfloat16* orow = p.dqkv + (int64_t(b) * S + kt * TILE + row) * (3 * int64_t(d)) + h * DH + half * 32;
+    // dK (x scale) and dV of this key tile (TMEM lane = key row); the last bar_dq wait covered all MMAs,
+    // so the Pd / dS tiles are free to stage them
     {
       uint32_t v[32];
+      float f[32];
       tmem_ld_32x32(t_row + C_DK + half * 32, v);
       tmem_ld_wait();
-      store_out32(orow + int64_t(d), v, p.scale * ik);
+      const float sk = p.scale * ik;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * sk;
+      store_row32(sDS, row, half * 32, f);
       tmem_ld_32x32(t_row + C_DV + half * 32, v);
       tmem_ld_wait();
-      store_out32(orow + 2 * int64_t(d), v, ik);
+#pragma unroll
+      for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * ik;
+      store_row32(sPd, row, half * 32, f);
     }
+    tc_fence_before();
+    fence_proxy_async_smem();
+    mbar_arrive(bar_out);
   }
   tc_fence_before();
   __syncthreads();
@@ -722,7 +755,7 @@ __global__ void __launch_bounds__(256) attn_dq_reduce_kernel(const __nv_bfloat16
 }
 
 static size_t fwd_smem(int nc) { return 1024 + size_t(1 + 2 * nc) * TILE_BYTES + 2 * P_BYTES + 2 * TILE * 4 + 64 + 256; }
-static size_t bwd_smem() { return 1024 + 6 * size_t(TILE_BYTES) + 2 * P_BYTES + 16 + 256; }
+static size_t bwd_smem() { return 1024 + 8 * size_t(TILE_BYTES) + 2 * P_BYTES + 16 + 256; }
 
 template <typename Kern>
 static int set_smem(Kern k, size_t bytes) {
@@ -813,6 +846,13 @@ extern "C" HSTD_API int hstd_attn_bwd(const void* qkv, const void* ctx, const vo
   if (int rc = get_tmap(&tk, base + d, DH, S, H, B, 3 * d, DH, S * 3 * d, TILE)) return rc;
   if (int rc = get_tmap(&tv, base + 2 * d, DH, S, H, B, 3 * d, DH, S * 3 * d, TILE)) return rc;
   if (int rc = get_tmap(&tdo, dctx, DH, S, H, B, d, DH, S * d, TILE)) return rc;
+  // outputs leave by TMA bulk stores: the dQ partials [S/128][B*S][d] seen as {d, S, B, key tile},
+  // dK / dV in the K / V slots of dqkv seen like the inputs
+  CUtensorMap tdqp, tdk, tdv;
+  __nv_bfloat16* gbase = static_cast<__nv_bfloat16*>(dqkv);
+  if (int rc = get_tmap(&tdqp, dq_part, d, S, B, S / TILE, d, S * d, int64_t(B) * S * d, TILE)) return rc;
+  if (int rc = get_tmap(&tdk, gbase + d, DH, S, H, B, 3 * d, DH, S * 3 * d, TILE)) return rc;
+  if (int rc = get_tmap(&tdv, gbase + 2 * d, DH, S, H, B, 3 * d, DH, S * 3 * d, TILE)) return rc;
   AttnParams p{};
   p.lse = const_cast<float*>(lse);
   p.delta = delta;
@@ -830,7 +870,7 @@ extern "C" HSTD_API int hstd_attn_bwd(const void* qkv, const void* ctx, const vo
       if (int rc = set_smem(attn_bwd_kernel<NQ_>, bwd_smem())) return rc;              \
       configured[NQ_] = true;                                                          \
     }                                                                                  \
-    launch_pdl(attn_bwd_kernel<NQ_>, grid, dim3(AT_THREADS), bwd_smem(), s, tq, tk, tv, tdo, p);     \
+    launch_pdl(attn_bwd_kernel<NQ_>, grid, dim3(AT_THREADS), bwd_smem(), s, tq, tk, tv, tdo, tdqp, tdk, tdv, p); \
     break;                                                                             \
   }
   switch (nq) {
