@@ -436,6 +436,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
                 const __grid_constant__ CUtensorMap tm_dqp, const __grid_constant__ CUtensorMap tm_dk,
                 const __grid_constant__ CUtensorMap tm_dv, const AttnParams p) {
   HSTD_PDL_PROLOGUE();
+  if (threadIdx.x == 0) HSTD_ATRACE(24);
   constexpr uint32_t TMEM_COLS = 512;
   constexpr uint32_t C_S = 0, C_DP = 128, C_DV = 256, C_DK = 320, C_DQ = 384;
   constexpr uint32_t IDESC_S = make_idesc_bf16(TILE, TILE, false, false);   // Q·Kᵀ, dO·Vᵀ
@@ -459,17 +460,54 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
   uint64_t* bar_dq = bars + 5;
   uint64_t* bar_dqread = bars + 6;  // dQ of this iteration has left TMEM and sits in its staging tile
   uint64_t* bar_out = bars + 7;     // dK / dV staged in smem
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+  uint64_t* bar_free = bars + 8;    // [2] every MMA reading Q/dO[buf] (and Pd, dS) of a query tile has completed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int kt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
   const int S = p.S;
   const int d = p.H * DH;
 
-  if (warp < AT_SOFTMAX_WARPS) build_mask_bits(sBits, p.key_mask + int64_t(b) * S + kt * TILE, 4, warp, lane);
+  // One synchronisation in the prologue.  The control warp looks at the key mask of this tile on
+  // its own (4 loads in flight per lane), so that barriers, TMEM and — above all — the first TMA
+  // loads are under way while the softmax warps are still balloting the mask bits.
+  bool any_key = true;
+  if (warp == AT_SOFTMAX_WARPS) {
+    const int32_t* km = p.key_mask + int64_t(b) * S + kt * TILE + lane;
+    const int32_t k0 = km[0], k1 = km[32], k2 = km[64], k3 = km[96];
+    if (lane == 0) {
+      tma_prefetch_desc(&tm_q); tma_prefetch_desc(&tm_k); tma_prefetch_desc(&tm_v); tma_prefetch_desc(&tm_do);
+      mbar_init(bar_kv, 1); mbar_init(&bar_q[0], 1); mbar_init(&bar_q[1], 1);
+      mbar_init(bar_sdp, 1); mbar_init(bar_pds, AT_ST); mbar_init(bar_dq, 1); mbar_init(bar_dqread, AT_ST);
+      mbar_init(bar_out, AT_ST); mbar_init(&bar_free[0], 1); mbar_init(&bar_free[1], 1);
+      tma_prefetch_desc(&tm_dqp); tma_prefetch_desc(&tm_dk); tma_prefetch_desc(&tm_dv);
+      fence_mbar_init();
+    }
+    any_key = __any_sync(0xffffffffu, (k0 | k1 | k2 | k3) != 0);
+    if (any_key) {
+      if (elect_one()) {
+        mbar_expect_tx(bar_kv, 2 * TILE_BYTES);
+        tma_load_4d(sK, &tm_k, bar_kv, 0, kt * TILE, h, b);
+        tma_load_4d(sV, &tm_v, bar_kv, 0, kt * TILE, h, b);
+        for (int i = 0; i < 2 && i < NQ; ++i) {
+          mbar_expect_tx(&bar_q[i], 2 * TILE_BYTES);
+          tma_load_4d(sQ + i * TILE_BYTES, &tm_q, &bar_q[i], 0, i * TILE, h, b);
+          tma_load_4d(sDO + i * TILE_BYTES, &tm_do, &bar_q[i], 0, i * TILE, h, b);
+        }
+      }
+      __syncwarp();
+      tmem_alloc(tmem_slot, TMEM_COLS);
+      tmem_relinquish();
+    }
+  } else {
+    build_mask_bits(sBits, p.key_mask + int64_t(b) * S + kt * TILE, 4, warp, lane);
+  }
+  tc_fence_before();
   __syncthreads();
+  tc_fence_after();
   if ((sBits[0] | sBits[1] | sBits[2] | sBits[3]) == 0) {
     // every key of this tile is padding: its dK, dV and its dQ contributions are exactly zero
+    // (the control warp reached the same verdict and has neither loaded nor allocated anything)
     const uint4 z = make_uint4(0, 0, 0, 0);
     for (int i = threadIdx.x; i < TILE * 8 * 2; i += AT_THREADS) {  // dK, dV: 128 rows x 128 B each
       const int which = i / (TILE * 8), r = (i / 8) % TILE, c = i % 8;
@@ -482,35 +520,10 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
     }
     return;
   }
-
-  if (warp == AT_SOFTMAX_WARPS) {
-    if (lane == 0) {
-      tma_prefetch_desc(&tm_q); tma_prefetch_desc(&tm_k); tma_prefetch_desc(&tm_v); tma_prefetch_desc(&tm_do);
-      mbar_init(bar_kv, 1); mbar_init(&bar_q[0], 1); mbar_init(&bar_q[1], 1);
-      mbar_init(bar_sdp, 1); mbar_init(bar_pds, AT_ST); mbar_init(bar_dq, 1); mbar_init(bar_dqread, AT_ST);
-      mbar_init(bar_out, AT_ST);
-      tma_prefetch_desc(&tm_dqp); tma_prefetch_desc(&tm_dk); tma_prefetch_desc(&tm_dv);
-      fence_mbar_init();
-    }
-    __syncwarp();
-    tmem_alloc(tmem_slot, TMEM_COLS);
-    tmem_relinquish();
-  }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
   const uint32_t tmem = *tmem_slot;
 
   if (warp == AT_SOFTMAX_WARPS) {
     if (elect_one()) {
-      mbar_expect_tx(bar_kv, 2 * TILE_BYTES);
-      tma_load_4d(sK, &tm_k, bar_kv, 0, kt * TILE, h, b);
-      tma_load_4d(sV, &tm_v, bar_kv, 0, kt * TILE, h, b);
-      for (int i = 0; i < 2 && i < NQ; ++i) {
-        mbar_expect_tx(&bar_q[i], 2 * TILE_BYTES);
-        tma_load_4d(sQ + i * TILE_BYTES, &tm_q, &bar_q[i], 0, i * TILE, h, b);
-        tma_load_4d(sDO + i * TILE_BYTES, &tm_do, &bar_q[i], 0, i * TILE, h, b);
-      }
       mbar_wait(bar_kv, 0);
       // descriptors once; per-MMA variation is a constant added to the 16-byte-unit address field
       const uint64_t dK_k = make_smem_desc_sw128(smem_u32(sK), 16, 1024);           // K as K-major B (Q·Kᵀ)
@@ -523,17 +536,36 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
       const uint64_t dQ_mn0 = make_smem_desc_sw128(smem_u32(sQ), TILE_BYTES, 1024);
       const uint64_t dDO_k0 = make_smem_desc_sw128(smem_u32(sDO), 16, 1024);
       const uint64_t dDO_mn0 = make_smem_desc_sw128(smem_u32(sDO), TILE_BYTES, 1024);
-      for (int i = 0; i < NQ; ++i) {
+      // The tensor pipe executes in issue order, so nothing here waits for an MMA group to finish
+      // before issuing the next one.  Per query tile i the order is
+      //     dQ_i  |  S, dP of tile i+1  |  dV, dK of tile i
+      // so the softmax warps get their next scores after ~1200 cycles while dV/dK (which only feed
+      // TMEM accumulators) run underneath the next softmax.  dQ is committed on its own barrier, the
+      // Pd/dS/Q/dO tiles of tile i are released by bar_free once dV/dK have completed.
+      auto issue_scores = [&](int i) {
         const int buf = i & 1;
         const uint64_t boff = uint64_t(buf) * (TILE_BYTES >> 4);
         mbar_wait(&bar_q[buf], (i >> 1) & 1);
+        HSTD_ATRACE(32 + 8 * i + 0);  // ctl: Q/dO tile landed
         tc_fence_after();
 #pragma unroll
         for (int k = 0; k < DH / 16; ++k) umma_bf16(tmem + C_S, dQ_k0 + boff + k * 2, dK_k + k * 2, IDESC_S, k > 0);
 #pragma unroll
         for (int k = 0; k < DH / 16; ++k) umma_bf16(tmem + C_DP, dDO_k0 + boff + k * 2, dV_k + k * 2, IDESC_S, k > 0);
         umma_commit(bar_sdp);
+      };
+      issue_scores(0);
+      for (int i = 0; i < NQ; ++i) {
+        const int buf = i & 1;
+        const uint64_t boff = uint64_t(buf) * (TILE_BYTES >> 4);
         if (i > 0) {
+          // operand tiles of the previous query tile are free once its dV/dK MMAs have completed
+          mbar_wait(&bar_free[buf ^ 1], ((i - 1) >> 1) & 1);
+          if (i + 1 < NQ) {
+            mbar_expect_tx(&bar_q[buf ^ 1], 2 * TILE_BYTES);
+            tma_load_4d(sQ + (buf ^ 1) * TILE_BYTES, &tm_q, &bar_q[buf ^ 1], 0, (i + 1) * TILE, h, b);
+            tma_load_4d(sDO + (buf ^ 1) * TILE_BYTES, &tm_do, &bar_q[buf ^ 1], 0, (i + 1) * TILE, h, b);
+          }
           // dQ partial of the previous query tile: staged by the softmax warps, stored by TMA from here
           mbar_wait(bar_dqread, (i - 1) & 1);
           tc_fence_after();
@@ -542,7 +574,19 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
           tma_store_wait_read_le1();  // the store of tile i-2 has read its staging buffer: tile i may overwrite it
         }
         mbar_wait(bar_pds, i & 1);
+        HSTD_ATRACE(32 + 8 * i + 1);  // ctl: Pm / dS' ready
         tc_fence_after();
+        // dQ_i = dS · K : reduction over the 128 keys (dS K-major: 4 k-steps per 64-key atom)
+#pragma unroll
+        for (int k = 0; k < TILE / 16; ++k)
+          umma_bf16(tmem + C_DQ, dDS_k + (k >> 2) * (TILE_BYTES >> 4) + (k & 3) * 2, dK_mn + k * (2048 >> 4), IDESC_Q, k > 0);
+        umma_commit(bar_dq);
+        if (i + 1 < NQ) {
+          issue_scores(i + 1);  // S/dP are free: the softmax warps arrived on bar_pds
+          // Measured: MMAs issued behind the score MMAs delay the arrival of their commit by ~800
+          // cycles, so dV/dK are held back until the scores are visible to the softmax warps.
+          mbar_wait(bar_sdp, (i + 1) & 1);
+        }
         // reduction over the 128 query rows of this tile: 8 k-steps of 16 rows = 2048 B each
 #pragma unroll
         for (int k = 0; k < TILE / 16; ++k)
@@ -550,18 +594,10 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
 #pragma unroll
         for (int k = 0; k < TILE / 16; ++k)
           umma_bf16(tmem + C_DK, dDS_mn + k * (2048 >> 4), dQ_mn0 + boff + k * (2048 >> 4), IDESC_T, (i > 0 || k > 0));
-        // dQ_i = dS · K : reduction over the 128 keys (dS K-major: 4 k-steps per 64-key atom)
-#pragma unroll
-        for (int k = 0; k < TILE / 16; ++k)
-          umma_bf16(tmem + C_DQ, dDS_k + (k >> 2) * (TILE_BYTES >> 4) + (k & 3) * 2, dK_mn + k * (2048 >> 4), IDESC_Q, k > 0);
-        umma_commit(bar_dq);
-        mbar_wait(bar_dq, i & 1);  // tiles Q/dO[buf], Pd, dS are free again
-        if (i + 2 < NQ) {
-          mbar_expect_tx(&bar_q[buf], 2 * TILE_BYTES);
-          tma_load_4d(sQ + buf * TILE_BYTES, &tm_q, &bar_q[buf], 0, (i + 2) * TILE, h, b);
-          tma_load_4d(sDO + buf * TILE_BYTES, &tm_do, &bar_q[buf], 0, (i + 2) * TILE, h, b);
-        }
+        umma_commit(&bar_free[buf]);
+        HSTD_ATRACE(32 + 8 * i + 2);  // ctl: second MMA group issued
       }
+      mbar_wait(&bar_free[(NQ - 1) & 1], ((NQ - 1) >> 1) & 1);  // dV / dK complete
       mbar_wait(bar_dqread, (NQ - 1) & 1);
       tma_store_4d(&tm_dqp, sDQ + ((NQ - 1) & 1) * TILE_BYTES, h * DH, (NQ - 1) * TILE, b, kt);
       tma_store_commit();
@@ -571,6 +607,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
       tma_store_4d(&tm_dv, sPd, 0, kt * TILE, h, b);
       tma_store_commit();
       tma_store_wait_read();  // smem is released at CTA exit
+      HSTD_ATRACE(26);
     }
   } else {
     const int quarter = warp & 3, half = warp >> 2;
@@ -585,18 +622,37 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
     const float ik = dr.active() ? dr.scale : 1.f;
     const float inv_ik = 1.f / ik;
     const uint64_t sc2 = pack2(scale2, scale2);
+    auto stage_dq = [&](int j) {
+      mbar_wait(bar_dq, j & 1);
+      if (threadIdx.x == 0) HSTD_ATRACE(32 + 8 * j + 6);  // dQ visible
+      tc_fence_after();
+      uint32_t v[32];
+      tmem_ld_32x32(t_row + C_DQ + half * 32, v);
+      tmem_ld_wait();
+      float f[32];
+      const float sc = p.scale * ik;
+#pragma unroll
+      for (int q = 0; q < 32; ++q) f[q] = __uint_as_float(v[q]) * sc;
+      store_row32(sDQ + (j & 1) * TILE_BYTES, row, half * 32, f);
+      tc_fence_before();
+      fence_proxy_async_smem();
+      mbar_arrive(bar_dqread);
+      if (threadIdx.x == 0) HSTD_ATRACE(32 + 8 * j + 7);  // dQ staged
+    };
     for (int i = 0; i < NQ; ++i) {
       const uint64_t srow = (uint64_t(b) * p.H + h) * S + uint64_t(i) * TILE + row;  // global score row
       const float lse2 = p.lse[srow] * LOG2E;
       const float nd = -p.delta[srow] * inv_ik;
       const uint64_t nl2 = pack2(-lse2, -lse2), nd2 = pack2(nd, nd);
       mbar_wait(bar_sdp, i & 1);
+      if (threadIdx.x == 0) HSTD_ATRACE(32 + 8 * i + 4);  // S / dP visible
       tc_fence_after();
 #pragma unroll 1
       for (int sbi = 0; sbi < 2; ++sbi) {
         const int sb = half * 2 + sbi;
         const uint32_t bits = sBits[sb];
         if (bits == 0) {
+          if (sbi == 0 && i > 0) mbar_wait(&bar_free[(i - 1) & 1], ((i - 1) >> 1) & 1);
           store_row32_zero(sPd, row, sb * 32);
           store_row32_zero(sDS, row, sb * 32);
           continue;
@@ -670,6 +726,9 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
           if (dr.active()) body(std::true_type{}, std::false_type{});
           else body(std::false_type{}, std::false_type{});
         }
+        // dV/dK of the previous query tile run underneath this softmax and still read Pd / dS: its
+        // "free" barrier (practically always complete by now) gates the first overwrite
+        if (sbi == 0 && i > 0) mbar_wait(&bar_free[(i - 1) & 1], ((i - 1) >> 1) & 1);
         {
           const uint32_t aoff = ((sb * 32) >> 6) * TILE_BYTES;
           const uint32_t chunk0 = ((sb * 32) & 63u) >> 3;
@@ -684,27 +743,16 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
       tc_fence_before();
       fence_proxy_async_smem();
       mbar_arrive(bar_pds);
-      // dQ partial of this (query tile, key tile): 32 of the 64 columns per thread, into the swizzled
+      if (threadIdx.x == 0) HSTD_ATRACE(32 + 8 * i + 5);  // Pm / dS' written
+      // dQ partial of this (query tile, key tile): 32 of the 64 columns per thread into the swizzled
       // staging tile; the control thread stores it with one TMA bulk store (per-thread row stores
       // touched 32 different lines per instruction and cost ~900 cycles per query tile)
-      mbar_wait(bar_dq, i & 1);
-      tc_fence_after();
-      {
-        uint32_t v[32];
-        tmem_ld_32x32(t_row + C_DQ + half * 32, v);
-        tmem_ld_wait();
-        float f[32];
-        const float sc = p.scale * ik;
-#pragma unroll
-        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * sc;
-        store_row32(sDQ + (i & 1) * TILE_BYTES, row, half * 32, f);
-      }
-      tc_fence_before();
-      fence_proxy_async_smem();
-      mbar_arrive(bar_dqread);
+      stage_dq(i);
     }
-    // dK (x scale) and dV of this key tile (TMEM lane = key row); the last bar_dq wait covered all MMAs,
-    // so the Pd / dS tiles are free to stage them
+    // dK (x scale) and dV of this key tile (TMEM lane = key row), once the last dV / dK MMAs have
+    // completed; the Pd / dS tiles are then free to stage them
+    mbar_wait(&bar_free[(NQ - 1) & 1], ((NQ - 1) >> 1) & 1);
+    tc_fence_after();
     {
       uint32_t v[32];
       float f[32];
@@ -723,6 +771,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
     tc_fence_before();
     fence_proxy_async_smem();
     mbar_arrive(bar_out);
+    if (threadIdx.x == 0) HSTD_ATRACE(25);  // dK / dV staged
   }
   tc_fence_before();
   __syncthreads();
@@ -776,7 +825,7 @@ static int check_shape(int B, int H, int S) {
 
 using namespace hstd;
 
-// Debug aid: device buffer of >= 32 int64 that CTA (0,0,0) of the following forward launches fills
+// Debug aid: device buffer of >= 64 int64 that CTA (0,0,0) of the following attention launches fills
 // with clock64() stamps (NULL switches it off).
 extern "C" HSTD_API void hstd_attn_set_trace(void* device_buffer) { g_attn_trace = static_cast<long long*>(device_buffer); }
 
@@ -861,6 +910,7 @@ extern "C" HSTD_API int hstd_attn_bwd(const void* qkv, const void* ctx, const vo
   p.key_mask = key_mask;
   p.st = st; p.p_drop = p_drop; p.site = site;
   p.B = B; p.H = H; p.S = S; p.scale = scale;
+  p.trace = g_attn_trace;
   const int nq = S / TILE;
   dim3 grid(nq, H, B);
   static bool configured[5] = {false, false, false, false, false};
