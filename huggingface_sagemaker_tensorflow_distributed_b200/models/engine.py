@@ -21,6 +21,8 @@ Keras fit/evaluate (scripts/train.py:117-123,145,170); the per-op mapping is SUR
 """
 from __future__ import annotations
 
+import os
+
 import math
 from dataclasses import dataclass, field
 from typing import Callable, Dict, List, Optional, Tuple
@@ -536,6 +538,15 @@ class EngineBackend:
     def _run(self, plan: Plan) -> None:
         if self.use_cuda_graph and plan.graph is not None:
             plan.graph.replay()
+            return
+        if os.environ.get("HSTD_NVTX") == "1":
+            # eager, one NVTX range per recorded op: readable timelines in Nsight
+            from ..utils.timers import nvtx_range
+
+            names = plan.names + ["dp/optimizer"] * (len(plan.ops) - len(plan.names))
+            for f, n in zip(plan.ops, names):
+                with nvtx_range(n):
+                    f()
             return
         for f in plan.ops:
             f()

@@ -27,6 +27,7 @@ import torch
 from . import checkpoint
 from .data import BatchedDataset
 from .models.configuration import EncoderConfig, resolve_config
+from .utils.timers import nvtx_range
 from .optim import Adam
 from .parallel import comm
 
@@ -140,7 +141,8 @@ class SequenceClassifier:
             for step, (feats, labels) in enumerate(dataset):
                 if step >= steps:
                     break
-                meter.update(self.backend.train_step(feats, labels))
+                with nvtx_range("train_step"):
+                    meter.update(self.backend.train_step(feats, labels))
                 if verbose and log_every > 0 and (step + 1) % log_every == 0:
                     r = meter.read()
                     dt = time.time() - t0
@@ -173,7 +175,8 @@ class SequenceClassifier:
         for step, (feats, labels) in enumerate(dataset):
             if step >= n:
                 break
-            meter.update(self.backend.eval_step(feats, labels))
+            with nvtx_range("eval_step"):
+                meter.update(self.backend.eval_step(feats, labels))
         r = meter.read()
         r.pop("count")
         self._sink({"event": "evaluate", **r})
