@@ -27,6 +27,17 @@ def _register(lib) -> None:
     lib.hstd_tok_special_ids.argtypes = [vp, vp]
     lib.hstd_tok_encode_batch.argtypes = [vp, C.POINTER(C.c_char_p), i32, i32, i32, vp, vp, vp, i32]
 
+    lib.hstd_bpe_create.argtypes = [C.c_char_p, C.c_char_p]
+    lib.hstd_bpe_create.restype = vp
+    lib.hstd_bpe_destroy.argtypes = [vp]
+    lib.hstd_bpe_destroy.restype = None
+    lib.hstd_bpe_vocab_size.argtypes = [vp]
+    lib.hstd_bpe_token_to_id.argtypes = [vp, C.c_char_p]
+    lib.hstd_bpe_id_to_token.argtypes = [vp, i32]
+    lib.hstd_bpe_id_to_token.restype = C.c_char_p
+    lib.hstd_bpe_special_ids.argtypes = [vp, vp]
+    lib.hstd_bpe_encode_batch.argtypes = [vp, C.POINTER(C.c_char_p), i32, i32, i32, vp, vp, vp, i32]
+
     lib.hstd_bucket_plan.argtypes = [vp, vp, i32, i64, vp, vp, vp, i32]
     lib.hstd_bucket_tracker_create.argtypes = [vp, vp, i32, i32]
     lib.hstd_bucket_tracker_create.restype = vp
@@ -92,6 +103,50 @@ class NativeWordPiece:
         rc = self._lib.hstd_tok_encode_batch(self._h, arr, n, int(max_len), int(add_special_tokens),
                                              ids.ctypes.data, mask.ctypes.data, lengths.ctypes.data, int(num_threads))
         _lib.check(rc, "hstd_tok_encode_batch")
+        return ids, mask, lengths
+
+
+class NativeBPE:
+    """Owns one ``hstd_bpe`` (byte-level BPE, RoBERTa / GPT-2 files).  Same surface as NativeWordPiece;
+    ``cls_id`` / ``sep_id`` are the <s> / </s> ids."""
+
+    def __init__(self, vocab_json: str, merges_txt: str):
+        self._lib = _lib.load()
+        self._h = self._lib.hstd_bpe_create(str(vocab_json).encode(), str(merges_txt).encode())
+        if not self._h:
+            raise _err("hstd_bpe_create")
+        sp = (C.c_int32 * 4)()
+        _lib.check(self._lib.hstd_bpe_special_ids(self._h, sp), "hstd_bpe_special_ids")
+        self.pad_id, self.unk_id, self.cls_id, self.sep_id = (int(x) for x in sp)
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            self._lib.hstd_bpe_destroy(h)
+
+    @property
+    def vocab_size(self) -> int:
+        return int(self._lib.hstd_bpe_vocab_size(self._h))
+
+    def token_to_id(self, token: str) -> int:
+        return int(self._lib.hstd_bpe_token_to_id(self._h, token.encode()))
+
+    def id_to_token(self, idx: int) -> Optional[str]:
+        s = self._lib.hstd_bpe_id_to_token(self._h, int(idx))
+        return None if s is None else s.decode(errors="replace")
+
+    def encode_batch(self, texts: Sequence[str], max_len: int, add_special_tokens: bool = True,
+                     num_threads: int = 0) -> Tuple[np.ndarray, np.ndarray, np.ndarray]:
+        n = len(texts)
+        ids = np.empty((n, max_len), dtype=np.int32)
+        mask = np.empty((n, max_len), dtype=np.int32)
+        lengths = np.empty((n,), dtype=np.int32)
+        if n == 0:
+            return ids, mask, lengths
+        arr = (C.c_char_p * n)(*[t.replace("\x00", " ").encode("utf-8", errors="replace") for t in texts])
+        rc = self._lib.hstd_bpe_encode_batch(self._h, arr, n, int(max_len), int(add_special_tokens),
+                                             ids.ctypes.data, mask.ctypes.data, lengths.ctypes.data, int(num_threads))
+        _lib.check(rc, "hstd_bpe_encode_batch")
         return ids, mask, lengths
 
 

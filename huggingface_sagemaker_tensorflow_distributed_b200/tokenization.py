@@ -11,8 +11,9 @@ that surface on top of the native C++ tokenizer in libhstd_b200.so (csrc/tokeniz
     model's size with the BERT special-token layout, so the text -> ids -> train -> save path is
     exercised end to end; ``source`` says which one was used.
 
-RoBERTa's byte-level BPE is not re-implemented natively; ``AutoTokenizer`` falls back to the HF
-tokenizer for a local RoBERTa directory and to the synthetic WordPiece vocabulary otherwise.
+``ByteLevelBPETokenizer`` is the same facade over the native byte-level BPE (csrc/bpe_tokenizer.cpp)
+for a directory with ``vocab.json`` + ``merges.txt`` (RoBERTa checkpoints).  For a RoBERTa hub name
+(no files, no network) ``AutoTokenizer`` serves the synthetic WordPiece vocabulary of the model's size.
 """
 from __future__ import annotations
 
@@ -290,6 +291,62 @@ class WordPieceTokenizer:
         return {"input_ids": ids.tolist(), "attention_mask": mask.tolist()}
 
 
+class ByteLevelBPETokenizer(WordPieceTokenizer):
+    """RoBERTa / GPT-2 tokenizer files (``vocab.json`` + ``merges.txt``) served by the native byte-level
+    BPE.  Inherits the calling conventions of ``WordPieceTokenizer``; <s> / </s> frame a sequence."""
+
+    vocab_files_names = {"vocab_file": "vocab.json", "merges_file": "merges.txt"}
+
+    def __init__(self, vocab_file: str, merges_file: str, model_max_length: int = 512, source: str = "vocab.json"):
+        from .ops.host import NativeBPE
+
+        self.vocab_file, self.merges_file = str(vocab_file), str(merges_file)
+        self.do_lower_case, self.strip_accents = False, None
+        self.model_max_length = int(model_max_length)
+        self.source = source
+        self._native = NativeBPE(self.vocab_file, self.merges_file)
+        self.pad_token_id, self.unk_token_id = self._native.pad_id, self._native.unk_id
+        self.cls_token_id, self.sep_token_id = self._native.cls_id, self._native.sep_id
+        self.bos_token_id, self.eos_token_id = self.cls_token_id, self.sep_token_id
+        self.pad_token, self.unk_token, self.cls_token, self.sep_token, self.mask_token = (
+            "<pad>", "<unk>", "<s>", "</s>", "<mask>")
+
+    @classmethod
+    def from_pretrained(cls, path: str, **kw) -> "ByteLevelBPETokenizer":
+        vocab, merges = os.path.join(path, "vocab.json"), os.path.join(path, "merges.txt")
+        if not (os.path.isfile(vocab) and os.path.isfile(merges)):
+            raise FileNotFoundError(f"{vocab} / {merges} not found")
+        cfg: Dict[str, object] = {}
+        cfg_path = os.path.join(path, "tokenizer_config.json")
+        if os.path.isfile(cfg_path):
+            with open(cfg_path) as fh:
+                cfg = json.load(fh)
+        mml = cfg.get("model_max_length", 512)
+        mml = 512 if not isinstance(mml, (int, float)) or mml > 1 << 20 else int(mml)
+        return cls(vocab, merges, model_max_length=int(kw.pop("model_max_length", mml)), source=vocab)
+
+    def save_pretrained(self, save_dir: str) -> List[str]:
+        import shutil
+
+        os.makedirs(save_dir, exist_ok=True)
+        out = []
+        for src, name in ((self.vocab_file, "vocab.json"), (self.merges_file, "merges.txt")):
+            dst = os.path.join(save_dir, name)
+            if os.path.abspath(src) != os.path.abspath(dst):
+                shutil.copyfile(src, dst)
+            out.append(dst)
+        cfg = {"tokenizer_class": "RobertaTokenizer", "model_max_length": self.model_max_length, "add_prefix_space": False,
+               "bos_token": "<s>", "eos_token": "</s>", "sep_token": "</s>", "cls_token": "<s>", "unk_token": "<unk>",
+               "pad_token": "<pad>", "mask_token": "<mask>", "hstd_source": self.source}
+        for name, payload in (("tokenizer_config.json", cfg),
+                              ("special_tokens_map.json", {k: v for k, v in cfg.items() if k.endswith("_token")})):
+            p = os.path.join(save_dir, name)
+            with open(p, "w") as fh:
+                json.dump(payload, fh, indent=2)
+            out.append(p)
+        return out
+
+
 class AutoTokenizer:
     """``AutoTokenizer.from_pretrained`` of the reference (scripts/train.py:69)."""
 
@@ -299,6 +356,8 @@ class AutoTokenizer:
         if name_or_path and os.path.isdir(name_or_path):
             if os.path.isfile(os.path.join(name_or_path, "vocab.txt")):
                 return WordPieceTokenizer.from_pretrained(name_or_path, **kw)
+            if os.path.isfile(os.path.join(name_or_path, "vocab.json")) and os.path.isfile(os.path.join(name_or_path, "merges.txt")):
+                return ByteLevelBPETokenizer.from_pretrained(name_or_path, **kw)
             try:  # byte-level BPE (RoBERTa) and anything else with local files: the HF implementation
                 from transformers import AutoTokenizer as HFAuto
 

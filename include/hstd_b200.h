@@ -287,6 +287,19 @@ int hstd_tok_special_ids(const hstd_tokenizer* tok, int32_t* out4);     /* pad, 
 int hstd_tok_encode_batch(const hstd_tokenizer* tok, const char* const* texts, int n, int max_len,
                           int add_special_tokens, int32_t* ids, int32_t* mask, int32_t* lengths, int num_threads);
 
+/* Byte-level BPE (RoBERTa / GPT-2 vocab.json + merges.txt): GPT-2 pre-tokenisation, byte -> printable
+ * code point mapping, lowest-rank-first merges, <s> ... </s> framing.  Same output contract as
+ * hstd_tok_encode_batch.  special ids: pad, unk, bos, eos. */
+typedef struct hstd_bpe hstd_bpe;
+hstd_bpe* hstd_bpe_create(const char* vocab_json_path, const char* merges_path);
+void hstd_bpe_destroy(hstd_bpe* tok);
+int hstd_bpe_vocab_size(const hstd_bpe* tok);
+int hstd_bpe_token_to_id(const hstd_bpe* tok, const char* token);
+const char* hstd_bpe_id_to_token(const hstd_bpe* tok, int id);
+int hstd_bpe_special_ids(const hstd_bpe* tok, int32_t* out4);
+int hstd_bpe_encode_batch(const hstd_bpe* tok, const char* const* texts, int n, int max_len,
+                          int add_special_tokens, int32_t* ids, int32_t* mask, int32_t* lengths, int num_threads);
+
 /* ------------------------------------------------------------------ host runtime: fusion-bucket manager (N1)
  * What Horovod's C++ core does with its tensor-fusion buffer (reached from reference
  * scripts/train.py:114): decide which gradients travel together and notice when a group is

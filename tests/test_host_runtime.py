@@ -84,6 +84,43 @@ def test_tokenizer_call_semantics_and_roundtrip(tmp_path):
     assert auto.vocab_size == 30522 and "synthetic" in auto.source
 
 
+def test_byte_level_bpe_matches_hf_tokenizers_library(tmp_path):
+    """RoBERTa-style vocab.json + merges.txt (trained offline on synthetic reviews by the `tokenizers`
+    library, which is also the oracle): same ids for ASCII, contractions, whitespace runs, Latin-1,
+    CJK and emoji; <s> ... </s> framing, pad id 1, truncation keeps </s>."""
+    tk = pytest.importorskip("tokenizers")
+    from huggingface_sagemaker_tensorflow_distributed_b200.tokenization import (AutoTokenizer, ByteLevelBPETokenizer,
+                                                                                 synthetic_reviews)
+
+    texts, _ = synthetic_reviews(200, seed=2)
+    extra = ["The movie was great, I'd say it's the best!  Really... 123 times better than café №5 — naïve?",
+             "hello world\n\nnew  lines\tand tabs  ", "it's they're we've I'm you'll he'd 'quoted' 'such", "", "   ", " x", "x ",
+             "a\n b", "Ünïcödé façade — “quoted” 中文 text… ok? 😀 emoji nbsp\u00a0here 3.14 1,000 x² ½"]
+    oracle = tk.ByteLevelBPETokenizer()
+    oracle.train_from_iterator(texts + extra * 5, vocab_size=1500, show_progress=False,
+                               special_tokens=["<s>", "<pad>", "</s>", "<unk>", "<mask>"])
+    oracle.save_model(str(tmp_path))
+    tok = AutoTokenizer.from_pretrained(str(tmp_path))
+    assert isinstance(tok, ByteLevelBPETokenizer) and tok.vocab_size == oracle.get_vocab_size()
+    assert (tok.cls_token_id, tok.pad_token_id, tok.sep_token_id, tok.unk_token_id) == (0, 1, 2, 3)
+    sample = texts[:60] + extra
+    ids, mask, lengths = tok._native.encode_batch(sample, 2048, add_special_tokens=False)
+    for r, text in enumerate(sample):
+        want = oracle.encode(text).ids
+        assert ids[r, : int(mask[r].sum())].tolist() == want, (r, text[:60])
+        assert lengths[r] == len(want)
+    enc = tok(["a great movie", "bad"], padding="longest")
+    assert enc["input_ids"][0][0] == 0 and enc["input_ids"][0][-1] == 2 and enc["input_ids"][1][-1] == 1
+    assert enc["attention_mask"][1][-1] == 0
+    short = tok(texts[:4], padding="max_length", max_length=16, return_tensors="np")
+    assert short["input_ids"].shape == (4, 16) and (short["input_ids"][:, 0] == 0).all() and (short["input_ids"][:, -1] == 2).all()
+    out = tmp_path / "saved"
+    files = tok.save_pretrained(str(out))
+    assert {os.path.basename(f) for f in files} == {"vocab.json", "merges.txt", "tokenizer_config.json", "special_tokens_map.json"}
+    again = AutoTokenizer.from_pretrained(str(out))
+    assert again(texts[:8], padding="longest") == tok(texts[:8], padding="longest")
+
+
 def test_text_data_source_is_reference_shaped():
     from huggingface_sagemaker_tensorflow_distributed_b200.data import build_datasets
     from huggingface_sagemaker_tensorflow_distributed_b200.models.configuration import resolve_config
