@@ -109,7 +109,7 @@ def test_byte_level_bpe_matches_hf_tokenizers_library(tmp_path):
         want = oracle.encode(text).ids
         assert ids[r, : int(mask[r].sum())].tolist() == want, (r, text[:60])
         assert lengths[r] == len(want)
-    enc = tok(["a great movie", "bad"], padding="longest")
+    enc = tok(["a great movie , really wonderful and moving from the first scene to the last", "bad"], padding="longest")
     assert enc["input_ids"][0][0] == 0 and enc["input_ids"][0][-1] == 2 and enc["input_ids"][1][-1] == 1
     assert enc["attention_mask"][1][-1] == 0
     short = tok(texts[:4], padding="max_length", max_length=16, return_tensors="np")
