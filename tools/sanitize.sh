@@ -9,6 +9,11 @@
 # partial tiles, split-K, S=128/256 attention with padding, dropout on).  racecheck knows nothing about the
 # async proxy (TMA / tcgen05 reads of smem): hazards it reports between a generic-proxy store and a later
 # mbarrier-ordered bulk operation are expected and listed as such in the summary.
+# NOTE (round 1): compute-sanitizer is closed on this GPU pool ("runs under it have left GPUs needing a
+# reset"); the script is kept for pools where it is available.  The substitutes used here: every kernel is
+# compared with a PyTorch fp32 statement of the same op on small and odd shapes (partial tiles, padding),
+# outputs are pre-filled with NaN / sentinels so unwritten or over-written regions show up, and the peer-flag
+# spins of the all-reduce carry a clock watchdog that turns a missing peer into an error word.
 set -u
 TOOL=${1:-memcheck}
 OUT=gpurun_out/sanitize_${TOOL}.log
