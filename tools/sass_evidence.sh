@@ -39,7 +39,7 @@ with open("profiles/sass/summary.txt", "w") as w:
         w.write(f"{d:<82s} " + " ".join(f"{k}={v}" for k, v in c.items() if v) + "\n")
 print(open("profiles/sass/summary.txt").read()[:3000])
 PY
-# full listing of the three flagship kernels
+# full listings: flagship tensor-core kernels + the fused row / head / optimizer kernels
 rm -f $OUT/*.sass
 python - <<'PY'
 import re
@@ -49,7 +49,10 @@ want = {"gemm_256x256_2sm_TN": "gemm_bf16_kernelILi256ELb0ELb0ELi2E", "gemm_wgra
         "gemm_192_1sm_TN": "gemm_bf16_kernelILi192ELb0ELb0ELi1E",
         "attn_fwd_S512": "attn_fwd_kernelILi4E", "attn_bwd_S512": "attn_bwd_kernelILi4E",
         "fused_allreduce_nvls_adamw_w8": "fused_allreduce_kernelILi8ELi2ELb1E",
-        "fused_allreduce_two_shot_adamw_w8": "fused_allreduce_kernelILi8ELi0ELb1E"}
+        "fused_allreduce_two_shot_adamw_w8": "fused_allreduce_kernelILi8ELi0ELb1E",
+        "ln_fwd_residual_dropout_d768": "ln_fwd_kernelILi3ELb0E", "ln_fwd_embedding_d768": "ln_fwd_kernelILi3ELb1E",
+        "ln_bwd_rows_d768": "ln_bwd_rows_kernelILi3E", "head_logits_xent": "head_logits_loss_kernel",
+        "adamw_flat": "adamw_flat_kernel"}
 for out, key in want.items():
     for f in funcs:
         if key in f.split("\n", 2)[0] + f.split("\n", 2)[1 if len(f.split("\n")) > 1 else 0]:
