@@ -24,7 +24,7 @@ import time
 sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 
 
-def parse():
+def parse(argv=None):
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
@@ -38,7 +38,7 @@ def parse():
     ap.add_argument("--no_graph", action="store_true")
     ap.add_argument("--dropout", type=float, default=None)
     ap.add_argument("--exposed_comm", action="store_true", help="also time a no-communication step")
-    return ap.parse_args()
+    return ap.parse_args(argv)
 
 
 def reference_arm(a) -> None:
