@@ -1,0 +1,302 @@
+"""Discrete-event model of the mbarrier / tcgen05.commit protocol of the attention backward kernel.
+
+Written after a reordering of csrc/attention_sm100.cu hung on the GPU although the protocol looked
+right on paper: a GPU hang costs minutes of budget, a model run costs nothing.  Agents are Python
+generators: the control thread, the softmax warps, the tensor pipe (in-order queue of MMA groups and
+commits) and the TMA engine (loads / stores with latency).  mbarriers follow the PTX rules, including
+the parity aliasing trap: ``try_wait.parity P`` is true iff the barrier's current phase parity != P,
+so a waiter that is overtaken by TWO completions waits forever.
+
+    python tools/protocol_sim.py            # checks the protocol variants below under random timing
+
+Each variant is run a few thousand times with randomised latencies; a deadlock (all agents blocked,
+no event pending) or a data hazard (a tile overwritten while a queued MMA / store still reads it)
+is reported with the trace tail.
+"""
+from __future__ import annotations
+
+import heapq
+import random
+import sys
+from typing import Callable, Dict, List, Optional
+
+
+class Barrier:
+    def __init__(self, name: str, count: int):
+        self.name, self.count, self.pending, self.phase = name, count, count, 0
+
+    def arrive(self) -> None:
+        self.pending -= 1
+        assert self.pending >= 0, f"{self.name}: more arrivals than the count"
+        if self.pending == 0:
+            self.phase += 1
+            self.pending = self.count
+
+    def test(self, parity: int) -> bool:
+        return (self.phase & 1) != parity
+
+
+class Sim:
+    def __init__(self, seed: int):
+        self.rng = random.Random(seed)
+        self.now = 0
+        self.events: list = []  # (time, seq, fn)
+        self.seq = 0
+        self.waiters: List[tuple] = []  # (agent name, generator, barrier, parity)
+        self.trace: List[str] = []
+        self.hazards: List[str] = []
+        self.live = 0
+        # resources whose readers must finish before a writer touches them: name -> set(reader tags)
+        self.readers: Dict[str, set] = {}
+
+    def log(self, msg: str) -> None:
+        self.trace.append(f"{self.now:7d}  {msg}")
+
+    def at(self, delay: int, fn: Callable[[], None]) -> None:
+        self.seq += 1
+        heapq.heappush(self.events, (self.now + max(0, delay), self.seq, fn))
+
+    def jitter(self, base: int, spread: float = 0.5) -> int:
+        return max(1, int(base * (1.0 + spread * (self.rng.random() * 2 - 1))))
+
+    # ---- resource tracking
+    def read_begin(self, res: str, tag: str) -> None:
+        self.readers.setdefault(res, set()).add(tag)
+
+    def read_end(self, res: str, tag: str) -> None:
+        self.readers.get(res, set()).discard(tag)
+
+    def write(self, res: str, who: str) -> None:
+        r = self.readers.get(res)
+        if r:
+            self.hazards.append(f"t={self.now}: {who} writes {res} while {sorted(r)} still read(s) it")
+
+    # ---- agents
+    def spawn(self, name: str, gen) -> None:
+        self.live += 1
+        self._step(name, gen)
+
+    def _step(self, name: str, gen) -> None:
+        try:
+            req = next(gen)
+        except StopIteration:
+            self.live -= 1
+            self.log(f"{name}: done")
+            return
+        kind = req[0]
+        if kind == "delay":
+            self.at(req[1], lambda: self._step(name, gen))
+        elif kind == "wait":
+            _, bar, parity = req
+            if bar.test(parity):
+                self.at(self.jitter(20), lambda: self._step(name, gen))
+            else:
+                self.waiters.append((name, gen, bar, parity))
+        else:
+            raise ValueError(kind)
+
+    def poke(self) -> None:
+        still = []
+        for (name, gen, bar, parity) in self.waiters:
+            if bar.test(parity):
+                self.at(self.jitter(20), lambda n=name, g=gen: self._step(n, g))
+            else:
+                still.append((name, gen, bar, parity))
+        self.waiters = still
+
+    def arrive(self, bar: Barrier, who: str) -> None:
+        before = bar.phase
+        bar.arrive()
+        if bar.phase != before:
+            self.log(f"{bar.name}: phase {before} complete (last arrival: {who})")
+            self.poke()
+
+    def run(self, limit: int = 10_000_000) -> Optional[str]:
+        while self.events:
+            t, _, fn = heapq.heappop(self.events)
+            self.now = t
+            fn()
+            if self.now > limit:
+                return "time limit"
+        if self.live > 0:
+            blocked = ", ".join(f"{n} on {b.name} parity {p} (phase {b.phase})" for n, _, b, p in self.waiters)
+            return f"DEADLOCK: {blocked}"
+        return None
+
+
+class TensorPipe:
+    """In-order execution of MMA groups; a commit arrives on its barrier when everything before it is done."""
+
+    def __init__(self, sim: Sim):
+        self.sim, self.queue, self.busy = sim, [], False
+
+    def mma(self, name: str, cycles: int, reads=(), writes=()) -> None:
+        for r in reads:
+            self.sim.read_begin(r, name)
+        self.queue.append(("mma", name, cycles, tuple(reads), tuple(writes)))
+        self._kick()
+
+    def commit(self, bar: Barrier) -> None:
+        self.queue.append(("commit", bar))
+        self._kick()
+
+    def _kick(self) -> None:
+        if self.busy or not self.queue:
+            return
+        item = self.queue.pop(0)
+        if item[0] == "commit":
+            self.sim.arrive(item[1], "tensor pipe commit")
+            self._kick()
+            return
+        _, name, cycles, reads, writes = item
+        self.busy = True
+        for w in writes:
+            self.sim.write(w, name)
+
+        def done():
+            for r in reads:
+                self.sim.read_end(r, name)
+            self.busy = False
+            self._kick()
+
+        self.sim.at(self.sim.jitter(cycles, 0.2), done)
+
+
+def attention_bwd(sim: Sim, NQ: int, variant: str, warps: int = 8) -> None:
+    """variant 'b4': dQ_i | scores_{i+1} (+wait) | dV,dK_i, dQ staged in the same iteration (committed code).
+    variant 'b5': scores_{i+1} (+wait) | dQ_i (double-buffered) | dV,dK_i, dQ_{i-1} staged after softmax_i, the
+                  control thread collecting dQ_{i-1} at the END of iteration i — hung on the GPU; the model
+                  shows why: bar_dqread completes phases i-1 AND i while the control thread is still issuing
+                  MMAs, so its parity wait for phase i-1 is overtaken (aliasing) and never returns.
+    variant 'b5fix': same, but dQ_{i-1} is collected BEFORE dQ_i is issued (phase i of bar_dqread needs
+                  bar_dq phase i, which is only committed after that wait)."""
+    B = lambda n, c=1: Barrier(n, c)
+    bar_q = [B("bar_q0"), B("bar_q1")]
+    bar_sdp, bar_pds, bar_dq = B("bar_sdp"), B("bar_pds", warps), B("bar_dq")
+    bar_dqread, bar_out = B("bar_dqread", warps), B("bar_out", warps)
+    bar_free = [B("bar_free0"), B("bar_free1")]
+    pipe = TensorPipe(sim)
+    b5like = variant in ("b5", "b5fix")
+    nstage = 3 if variant == "b5" else 2  # the fixed order is hazard-free with two staging tiles
+
+    def tma_load(bar: Barrier, res: str, who: str):
+        sim.write(res, who)
+        sim.at(sim.jitter(900), lambda: sim.arrive(bar, who))
+
+    def tma_store(res: str, tag: str):
+        sim.read_begin(res, tag)
+        sim.at(sim.jitter(500), lambda: sim.read_end(res, tag))
+
+    def control():
+        for i in range(min(2, NQ)):
+            tma_load(bar_q[i], f"QdO{i}", f"load tile {i}")
+        yield ("delay", 50)
+
+        def scores(i):
+            buf = i & 1
+            yield ("wait", bar_q[buf], (i >> 1) & 1)
+            pipe.mma(f"scores{i}", 600, reads=(f"QdO{buf}",), writes=("SdP",))
+            pipe.commit(bar_sdp)
+            yield ("delay", sim.jitter(380))
+
+        yield from scores(0)
+        for i in range(NQ):
+            buf = i & 1
+            if i > 0:
+                yield ("wait", bar_free[buf ^ 1], ((i - 1) >> 1) & 1)
+                if i + 1 < NQ:
+                    tma_load(bar_q[buf ^ 1], f"QdO{buf ^ 1}", f"load tile {i + 1}")
+                if variant == "b4":
+                    yield ("wait", bar_dqread, (i - 1) & 1)
+                    tma_store(f"sDQ{(i - 1) % nstage}", f"store dQ{i - 1}")
+                    yield ("delay", 40)
+            yield ("wait", bar_pds, i & 1)
+            if variant == "b4":
+                pipe.mma(f"dQ{i}", 400, reads=("PdDS",), writes=("tDQ0",))
+                pipe.commit(bar_dq)
+                yield ("delay", sim.jitter(380))
+                if i + 1 < NQ:
+                    yield from scores(i + 1)
+                    yield ("wait", bar_sdp, (i + 1) & 1)
+            else:
+                if i + 1 < NQ:
+                    yield from scores(i + 1)
+                    yield ("wait", bar_sdp, (i + 1) & 1)
+                if variant == "b5fix" and i > 0:
+                    yield ("wait", bar_dqread, (i - 1) & 1)
+                    tma_store(f"sDQ{(i - 1) % nstage}", f"store dQ{i - 1}")
+                    yield ("delay", 40)
+                pipe.mma(f"dQ{i}", 400, reads=("PdDS",), writes=(f"tDQ{buf}",))
+                pipe.commit(bar_dq)
+                yield ("delay", sim.jitter(380))
+            pipe.mma(f"dVdK{i}", 750, reads=("PdDS", f"QdO{buf}"))
+            pipe.commit(bar_free[buf])
+            yield ("delay", sim.jitter(700))
+            if variant == "b5" and i > 0:
+                yield ("wait", bar_dqread, (i - 1) & 1)
+                tma_store(f"sDQ{(i - 1) % nstage}", f"store dQ{i - 1}")
+                yield ("delay", 40)
+        yield ("wait", bar_free[(NQ - 1) & 1], ((NQ - 1) >> 1) & 1)
+        yield ("wait", bar_dqread, (NQ - 1) & 1)
+        tma_store(f"sDQ{(NQ - 1) % nstage}", f"store dQ{NQ - 1}")
+        yield ("wait", bar_out, 0)
+
+    def softmax(w: int):
+        def stage_dq(j):
+            yield ("wait", bar_dq, j & 1)
+            tag = f"w{w} reads tDQ of tile {j}"
+            res = f"tDQ{j & 1}" if b5like else "tDQ0"
+            sim.read_begin(res, tag)
+            yield ("delay", sim.jitter(300))
+            sim.read_end(res, tag)
+            sim.write(f"sDQ{j % nstage}", f"w{w} stages dQ{j}")
+            yield ("delay", 50)
+            sim.arrive(bar_dqread, f"w{w}")
+
+        for i in range(NQ):
+            yield ("wait", bar_sdp, i & 1)
+            tag = f"w{w} reads SdP of tile {i}"
+            sim.read_begin("SdP", tag)
+            yield ("delay", sim.jitter(1300))
+            if i > 0:
+                yield ("wait", bar_free[(i - 1) & 1], ((i - 1) >> 1) & 1)
+            sim.write("PdDS", f"w{w} softmax{i}")
+            yield ("delay", sim.jitter(1300))
+            sim.read_end("SdP", tag)
+            sim.arrive(bar_pds, f"w{w}")
+            if variant == "b4":
+                yield from stage_dq(i)
+            elif i > 0:
+                yield from stage_dq(i - 1)
+        if b5like:
+            yield from stage_dq(NQ - 1)
+        yield ("wait", bar_free[(NQ - 1) & 1], ((NQ - 1) >> 1) & 1)
+        yield ("delay", sim.jitter(400))
+        sim.arrive(bar_out, f"w{w}")
+
+    sim.spawn("control", control())
+    for w in range(warps):
+        sim.spawn(f"softmax{w}", softmax(w))
+
+
+def check(variant: str, NQ: int, runs: int = 2000) -> bool:
+    ok = True
+    for seed in range(runs):
+        sim = Sim(seed)
+        attention_bwd(sim, NQ, variant)
+        err = sim.run()
+        if err or sim.hazards:
+            ok = False
+            print(f"[{variant} NQ={NQ} seed={seed}] {err or ''} {'; '.join(sim.hazards[:3])}")
+            print("\n".join(sim.trace[-12:]))
+            break
+    print(f"{variant} NQ={NQ}: {'no deadlock / hazard in ' + str(runs) + ' runs' if ok else 'FAILED'}")
+    return ok
+
+
+if __name__ == "__main__":
+    good = True
+    for variant in ("b4", "b5", "b5fix"):
+        for NQ in (1, 2, 3, 4):
+            good &= check(variant, NQ, runs=int(sys.argv[1]) if len(sys.argv) > 1 else 2000)
+    sys.exit(0)  # 'b5' is expected to fail: it documents the hang
