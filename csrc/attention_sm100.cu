@@ -438,7 +438,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
   HSTD_PDL_PROLOGUE();
   if (threadIdx.x == 0) HSTD_ATRACE(24);
   constexpr uint32_t TMEM_COLS = 512;
-  constexpr uint32_t C_S = 0, C_DP = 128, C_DV = 256, C_DK = 320, C_DQ = 384;
+  constexpr uint32_t C_S = 0, C_DP = 128, C_DV = 256, C_DK = 320, C_DQ = 384;  // dQ: two buffers of 64 columns
   constexpr uint32_t IDESC_S = make_idesc_bf16(TILE, TILE, false, false);   // Q·Kᵀ, dO·Vᵀ
   constexpr uint32_t IDESC_T = make_idesc_bf16(TILE, DH, true, true);       // Pdᵀ·dO, dSᵀ·Q
   constexpr uint32_t IDESC_Q = make_idesc_bf16(TILE, DH, false, true);      // dS·K
@@ -566,27 +566,33 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
             tma_load_4d(sQ + (buf ^ 1) * TILE_BYTES, &tm_q, &bar_q[buf ^ 1], 0, (i + 1) * TILE, h, b);
             tma_load_4d(sDO + (buf ^ 1) * TILE_BYTES, &tm_do, &bar_q[buf ^ 1], 0, (i + 1) * TILE, h, b);
           }
-          // dQ partial of the previous query tile: staged by the softmax warps, stored by TMA from here
-          mbar_wait(bar_dqread, (i - 1) & 1);
-          tc_fence_after();
-          tma_store_4d(&tm_dqp, sDQ + ((i - 1) & 1) * TILE_BYTES, h * DH, (i - 1) * TILE, b, kt);
-          tma_store_commit();
-          tma_store_wait_read_le1();  // the store of tile i-2 has read its staging buffer: tile i may overwrite it
         }
         mbar_wait(bar_pds, i & 1);
         HSTD_ATRACE(32 + 8 * i + 1);  // ctl: Pm / dS' ready
         tc_fence_after();
-        // dQ_i = dS · K : reduction over the 128 keys (dS K-major: 4 k-steps per 64-key atom)
-#pragma unroll
-        for (int k = 0; k < TILE / 16; ++k)
-          umma_bf16(tmem + C_DQ, dDS_k + (k >> 2) * (TILE_BYTES >> 4) + (k & 3) * 2, dK_mn + k * (2048 >> 4), IDESC_Q, k > 0);
-        umma_commit(bar_dq);
         if (i + 1 < NQ) {
           issue_scores(i + 1);  // S/dP are free: the softmax warps arrived on bar_pds
           // Measured: MMAs issued behind the score MMAs delay the arrival of their commit by ~800
-          // cycles, so dV/dK are held back until the scores are visible to the softmax warps.
+          // cycles, so everything else is held back until the scores are visible to the softmax warps.
           mbar_wait(bar_sdp, (i + 1) & 1);
         }
+        if (i > 0) {
+          // dQ partial of the previous query tile: staged by the softmax warps right after their softmax
+          // of this tile, stored by TMA from here.  This wait MUST precede the commit of dQ_i below:
+          // phase i of bar_dqread needs bar_dq phase i, so the parity wait for phase i-1 cannot be
+          // overtaken by two completions (tools/protocol_sim.py reproduces the hang of the other order).
+          mbar_wait(bar_dqread, (i - 1) & 1);
+          tma_store_4d(&tm_dqp, sDQ + ((i - 1) & 1) * TILE_BYTES, h * DH, (i - 1) * TILE, b, kt);
+          tma_store_commit();
+          tma_store_wait_read_le1();  // the store of tile i-2 has read the staging tile that dQ_i will use
+        }
+        // dQ_i = dS · K : reduction over the 128 keys (dS K-major: 4 k-steps per 64-key atom), into
+        // the dQ buffer of this parity (the other one is being read out by the softmax warps)
+#pragma unroll
+        for (int k = 0; k < TILE / 16; ++k)
+          umma_bf16(tmem + C_DQ + buf * DH, dDS_k + (k >> 2) * (TILE_BYTES >> 4) + (k & 3) * 2, dK_mn + k * (2048 >> 4),
+                    IDESC_Q, k > 0);
+        umma_commit(bar_dq);
         // reduction over the 128 query rows of this tile: 8 k-steps of 16 rows = 2048 B each
 #pragma unroll
         for (int k = 0; k < TILE / 16; ++k)
@@ -627,7 +633,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
       if (threadIdx.x == 0) HSTD_ATRACE(32 + 8 * j + 6);  // dQ visible
       tc_fence_after();
       uint32_t v[32];
-      tmem_ld_32x32(t_row + C_DQ + half * 32, v);
+      tmem_ld_32x32(t_row + C_DQ + (j & 1) * DH + half * 32, v);
       tmem_ld_wait();
       float f[32];
       const float sc = p.scale * ik;
@@ -744,11 +750,13 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant_
       fence_proxy_async_smem();
       mbar_arrive(bar_pds);
       if (threadIdx.x == 0) HSTD_ATRACE(32 + 8 * i + 5);  // Pm / dS' written
-      // dQ partial of this (query tile, key tile): 32 of the 64 columns per thread into the swizzled
-      // staging tile; the control thread stores it with one TMA bulk store (per-thread row stores
-      // touched 32 different lines per instruction and cost ~900 cycles per query tile)
-      stage_dq(i);
+      // dQ partial of the PREVIOUS query tile (its MMA ran underneath the softmax above, into the dQ
+      // buffer of its parity): 32 of the 64 columns per thread into the swizzled staging tile; the
+      // control thread stores it with one TMA bulk store (per-thread row stores touched 32 different
+      // lines per instruction and cost ~900 cycles per query tile)
+      if (i > 0) stage_dq(i - 1);
     }
+    stage_dq(NQ - 1);
     // dK (x scale) and dV of this key tile (TMEM lane = key row), once the last dV / dK MMAs have
     // completed; the Pd / dS tiles are then free to stage them
     mbar_wait(&bar_free[(NQ - 1) & 1], ((NQ - 1) >> 1) & 1);
