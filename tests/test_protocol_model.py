@@ -1,0 +1,32 @@
+"""The barrier protocol of the attention backward kernel, checked in the discrete-event model
+(tools/protocol_sim.py): the order that is in the tree must be free of deadlocks and tile hazards
+under random timing, and the order that hung on the GPU must still be caught by the model."""
+import os
+import sys
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+
+
+def _run(variant, NQ, seeds):
+    import protocol_sim as ps
+
+    for seed in seeds:
+        sim = ps.Sim(seed)
+        ps.attention_bwd(sim, NQ, variant)
+        err = sim.run()
+        if err or sim.hazards:
+            return err or sim.hazards[0]
+    return None
+
+
+def test_order_in_the_tree_is_deadlock_and_hazard_free():
+    for NQ in (1, 2, 3, 4):
+        assert _run("b5fix", NQ, range(150)) is None
+        assert _run("b4", NQ, range(50)) is None
+
+
+def test_model_catches_the_parity_overrun_that_hung_on_the_gpu():
+    assert _run("b5", 1, range(20)) is None  # one query tile: nothing to overrun
+    for NQ in (2, 4):
+        err = _run("b5", NQ, range(5))
+        assert err is not None and "DEADLOCK" in err and "bar_dqread" in err
