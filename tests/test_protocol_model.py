@@ -30,3 +30,23 @@ def test_model_catches_the_parity_overrun_that_hung_on_the_gpu():
     for NQ in (2, 4):
         err = _run("b5", NQ, range(5))
         assert err is not None and "DEADLOCK" in err and "bar_dqread" in err
+
+
+def test_allreduce_flag_protocol_orders_gradient_reads_and_weight_writes():
+    """K9 signal-flag protocol: monotone per-(rank, peer) flag words with start and end
+    barriers.  The model must see no stale / overwritten gradient read, no forward on half-updated
+    weights and no deadlock — and must notice when the end barrier is taken away."""
+    import protocol_sim as ps
+
+    for world in (2, 8):
+        for seed in range(60):
+            sim = ps.Sim(seed)
+            ps.allreduce_protocol(sim, world, steps=4)
+            assert sim.run() is None and not sim.hazards, (world, seed, sim.hazards[:2])
+    broken = 0
+    for seed in range(40):
+        sim = ps.Sim(seed)
+        ps.allreduce_protocol(sim, 4, steps=4, break_end_barrier=True)
+        sim.run()
+        broken += bool(sim.hazards)
+    assert broken > 20  # without the end barrier most timings expose a violation

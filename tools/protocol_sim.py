@@ -294,9 +294,106 @@ def check(variant: str, NQ: int, runs: int = 2000) -> bool:
     return ok
 
 
+# ---------------------------------------------------------------------------------------------
+# Gradient all-reduce flag protocol (csrc/allreduce_sm100.cu: block_barrier + epochs), K9
+# ---------------------------------------------------------------------------------------------
+def allreduce_protocol(sim: Sim, world: int, steps: int, break_end_barrier: bool = False) -> None:
+    """Every rank runs, per training step: backward (writes its gradient bucket) -> fused kernel:
+    start barrier (value 2e+1) | reduce-scatter by peer loads of everybody's gradients | AdamW on the
+    owned slice | all-gather by peer stores of the new weights | end barrier (2e+2) | epoch += 1 ->
+    next forward (reads its weight arena).  Flags are monotone values compared with >=, written with
+    release and read with acquire semantics, one word per (rank, peer).  Checked invariants:
+      * a rank never reads a peer gradient of another step (stale or already overwritten);
+      * a rank never starts a forward before every slice of its weights carries the current step;
+      * no deadlock.
+    break_end_barrier=True removes the end barrier (the model must then report a violation)."""
+    flags = [[0] * world for _ in range(world)]     # flags[r][p]: written by rank p into rank r's memory
+    grad_ver = [-1] * world                         # step whose gradients rank r's bucket holds
+    weight_ver = [[-1] * world for _ in range(world)]  # weight_ver[r][s]: step of slice s in rank r's arena
+    waiting: List[tuple] = []                       # (rank gen name, gen, r, peer, val)
+
+    def poll():
+        still = []
+        for (name, gen, r, peer, val) in waiting:
+            if flags[r][peer] >= val:
+                sim.at(sim.jitter(30), lambda n=name, g=gen: step_agent(n, g))
+            else:
+                still.append((name, gen, r, peer, val))
+        waiting[:] = still
+
+    def step_agent(name, gen):
+        try:
+            req = next(gen)
+        except StopIteration:
+            sim.live -= 1
+            return
+        if req[0] == "delay":
+            sim.at(req[1], lambda: step_agent(name, gen))
+        else:  # ("flagwait", r, peer, val)
+            _, r, peer, val = req
+            if flags[r][peer] >= val:
+                sim.at(sim.jitter(30), lambda: step_agent(name, gen))
+            else:
+                waiting.append((name, gen, r, peer, val))
+
+    def signal(r, peer, val):
+        def land():
+            flags[peer][r] = max(flags[peer][r], val)
+            poll()
+        sim.at(sim.jitter(60), land)  # NVLink store latency
+
+    def barrier(r, val):
+        for peer in range(world):
+            signal(r, peer, val)
+        for peer in range(world):
+            yield ("flagwait", r, peer, val)
+
+    def rank(r):
+        for t in range(steps):
+            if t > 0:  # forward of step t reads the weights produced by step t-1
+                for s in range(world):
+                    if weight_ver[r][s] != t - 1:
+                        sim.hazards.append(f"rank {r} starts forward {t} with slice {s} at version {weight_ver[r][s]}")
+            yield ("delay", sim.jitter(3000, 0.8))  # forward + backward, very uneven between ranks
+            grad_ver[r] = t
+            yield from barrier(r, 2 * t + 1)
+            for peer in range(world):  # reduce-scatter: peer loads
+                yield ("delay", sim.jitter(40))
+                if grad_ver[peer] != t:
+                    sim.hazards.append(f"rank {r} step {t} reads rank {peer}'s gradients of step {grad_ver[peer]}")
+            yield ("delay", sim.jitter(200))  # AdamW on the owned slice
+            for peer in range(world):  # all-gather: peer stores of slice r
+                def land(p=peer, tt=t):
+                    weight_ver[p][r] = tt
+                sim.at(sim.jitter(60), land)
+            yield ("delay", 80)  # __threadfence_system(): the stores above are performed before the release below
+            if not break_end_barrier:
+                yield from barrier(r, 2 * t + 2)
+
+    for r in range(world):
+        sim.live += 1
+        step_agent(f"rank{r}", rank(r))
+
+
+def check_allreduce(world: int, runs: int = 300) -> bool:
+    ok = True
+    for seed in range(runs):
+        sim = Sim(seed)
+        allreduce_protocol(sim, world, steps=4)
+        err = sim.run()
+        if err or sim.hazards:
+            ok = False
+            print(f"[allreduce world={world} seed={seed}] {err or ''} {'; '.join(sim.hazards[:3])}")
+            break
+    print(f"allreduce flags world={world}: {'no deadlock / hazard in ' + str(runs) + ' runs' if ok else 'FAILED'}")
+    return ok
+
+
 if __name__ == "__main__":
     good = True
     for variant in ("b4", "b5", "b5fix"):
         for NQ in (1, 2, 3, 4):
             good &= check(variant, NQ, runs=int(sys.argv[1]) if len(sys.argv) > 1 else 2000)
+    for world in (2, 4, 8):
+        check_allreduce(world, 200)
     sys.exit(0)  # 'b5' is expected to fail: it documents the hang
