@@ -18,6 +18,13 @@
 //     dV += Pdᵀ·dO_i, dK += dSᵀ·Q_i (accumulated in TMEM over i), dQ_i = dS·K written as a
 //     per-key-tile partial; a small kernel sums the partials.  The same smem image of a tile
 //     serves as K-major A operand and as MN-major B operand (only the descriptors differ).
+//     MMA issue order per query tile: scores of tile i+1 | dQ_i (two TMEM buffers, read out under
+//     the softmax of tile i+1) | dV, dK; commit barriers release operand tiles, the control thread
+//     never waits for an MMA to finish.  tools/protocol_sim.py models this barrier protocol.
+//  Softmax loops are written for the pipes that bound them (MUFU ex2 and the half-rate integer
+//  ALU): packed FFMA2/FADD2/FMUL2, dropout keep flags four bytes at a time applied by AND, 1/keep
+//  folded into the epilogue scales, one straight-line block per (dropout, full sub-block) variant.
+//  Every output (O, dQ partials, dK, dV) is staged in swizzled smem and stored by TMA.
 #include <string>
 #include <type_traits>
 

@@ -196,6 +196,10 @@ int hstd_attn_bwd(const void* qkv, const void* ctx, const void* dctx, const floa
                   void* dqkv, void* workspace, int B, int H, int S, float scale, float p_drop, uint32_t site,
                   const hstd_step_state* st, void* stream);
 int64_t hstd_attn_bwd_workspace_bytes(int B, int H, int S);
+/* Debug aids (tools/attn_trace.py, tools/gemm_trace.py): a device buffer of >= 64 / >= 512 int64 that CTA 0 of
+ * the following attention / GEMM launches fills with clock64() stamps of its phases; NULL switches it off. */
+void hstd_attn_set_trace(void* device_buffer);
+void hstd_gemm_set_trace(void* device_buffer);
 
 /* ------------------------------------------------------------------ embeddings (K1)
  * position ids: mode 0 = arange(S); mode 1 = RoBERTa (cumsum(ids != pad) * (ids != pad) + pad). */
