@@ -247,8 +247,27 @@ class WordPieceTokenizer:
         return [self._native.id_to_token(int(i)) for i in ids]
 
     def tokenize(self, text: str) -> List[str]:
-        ids, mask, _ = self._native.encode_batch([text], max_len=max(8, 2 * len(text) + 2), add_special_tokens=False)
+        ids, mask, _ = self._native.encode_batch([text], max_len=max(8, 4 * len(text) + 2), add_special_tokens=False)
         return self.convert_ids_to_tokens(ids[0, : int(mask[0].sum())])
+
+    def _special_ids(self) -> set:
+        return {self.pad_token_id, self.cls_token_id, self.sep_token_id}
+
+    def decode(self, ids: Sequence[int], skip_special_tokens: bool = True) -> str:
+        """Inverse of the encoder up to the normalisation it applied (WordPiece: lower-casing, accent
+        stripping, whitespace; continuation pieces are glued back, punctuation stays space-separated)."""
+        toks = [self._native.id_to_token(int(i)) or self.unk_token for i in ids
+                if not (skip_special_tokens and int(i) in self._special_ids())]
+        out: List[str] = []
+        for t in toks:
+            if t.startswith("##") and out:
+                out[-1] += t[2:]
+            else:
+                out.append(t)
+        return " ".join(out)
+
+    def batch_decode(self, batch: Sequence[Sequence[int]], skip_special_tokens: bool = True) -> List[str]:
+        return [self.decode(r, skip_special_tokens) for r in batch]
 
     # ------------------------------------------------------------------ encoding
     def encode_dense(self, texts: Sequence[str], max_length: Optional[int] = None, padding: str = "max_length",
@@ -291,6 +310,9 @@ class WordPieceTokenizer:
         return {"input_ids": ids.tolist(), "attention_mask": mask.tolist()}
 
 
+_BPE_UNICODE_TO_BYTE: Optional[Dict[str, int]] = None
+
+
 class ByteLevelBPETokenizer(WordPieceTokenizer):
     """RoBERTa / GPT-2 tokenizer files (``vocab.json`` + ``merges.txt``) served by the native byte-level
     BPE.  Inherits the calling conventions of ``WordPieceTokenizer``; <s> / </s> frame a sequence."""
@@ -310,6 +332,24 @@ class ByteLevelBPETokenizer(WordPieceTokenizer):
         self.bos_token_id, self.eos_token_id = self.cls_token_id, self.sep_token_id
         self.pad_token, self.unk_token, self.cls_token, self.sep_token, self.mask_token = (
             "<pad>", "<unk>", "<s>", "</s>", "<mask>")
+
+    def decode(self, ids: Sequence[int], skip_special_tokens: bool = True) -> str:
+        """Exact inverse for byte-level BPE: tokens are concatenated and every code point is mapped
+        back to its byte."""
+        global _BPE_UNICODE_TO_BYTE
+        if _BPE_UNICODE_TO_BYTE is None:
+            keep = list(range(33, 127)) + list(range(161, 173)) + list(range(174, 256))
+            table, extra = {}, 0
+            for b in range(256):
+                if b in keep:
+                    table[chr(b)] = b
+                else:
+                    table[chr(256 + extra)] = b
+                    extra += 1
+            _BPE_UNICODE_TO_BYTE = table
+        text = "".join(self._native.id_to_token(int(i)) or "" for i in ids
+                       if not (skip_special_tokens and int(i) in self._special_ids()))
+        return bytes(_BPE_UNICODE_TO_BYTE.get(ch, ord("?")) for ch in text).decode("utf-8", errors="replace")
 
     @classmethod
     def from_pretrained(cls, path: str, **kw) -> "ByteLevelBPETokenizer":

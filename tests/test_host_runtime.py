@@ -72,6 +72,8 @@ def test_tokenizer_call_semantics_and_roundtrip(tmp_path):
     single = tok("a great movie")
     assert single["input_ids"][0] == 101 and single["input_ids"][-1] == 102 and all(single["attention_mask"])
     assert tok.convert_ids_to_tokens(single["input_ids"])[1:-1] == tok.tokenize("a great movie")
+    assert tok.decode(single["input_ids"]) == "a great movie"
+    assert tok.batch_decode(tok(["Wonderful , moving film !", "BAD"])["input_ids"]) == ["wonderful , moving film !", "bad"]
     # save_pretrained / from_pretrained (scripts/train.py:183) through the Auto class
     files = tok.save_pretrained(tmp_path)
     assert {os.path.basename(f) for f in files} == {"vocab.txt", "tokenizer_config.json", "special_tokens_map.json"}
@@ -119,6 +121,9 @@ def test_byte_level_bpe_matches_hf_tokenizers_library(tmp_path):
     assert {os.path.basename(f) for f in files} == {"vocab.json", "merges.txt", "tokenizer_config.json", "special_tokens_map.json"}
     again = AutoTokenizer.from_pretrained(str(out))
     assert again(texts[:8], padding="longest") == tok(texts[:8], padding="longest")
+    # byte-level BPE is lossless: decode(encode(x)) == x, including the odd ones
+    for text in extra + texts[:5]:
+        assert tok.decode(tok(text)["input_ids"]) == text
 
 
 def test_text_data_source_is_reference_shaped():
