@@ -3,6 +3,7 @@
 // UMMA shared-memory + instruction descriptors.  Everything here is inline PTX;
 // no CUTLASS/CuTe types are used.
 #pragma once
+#include <cstdio>
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
@@ -51,9 +52,28 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
+// Development builds (-DHSTD_MBAR_WATCHDOG, `python -m <package>.build --watchdog`) turn a barrier that
+// never completes — a protocol bug such as a parity overrun — into a trap after ~2 s instead of a hung
+// GPU: a hang costs minutes of box time, a trap fails the test at once.  Off by default: the production
+// wait is the bare try_wait loop.
+#ifndef HSTD_MBAR_TIMEOUT_CYCLES
+#define HSTD_MBAR_TIMEOUT_CYCLES 4000000000ll
+#endif
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+#ifdef HSTD_MBAR_WATCHDOG
+  if (mbar_try_wait(bar, parity)) return;
+  const long long t0 = clock64();
+  while (!mbar_try_wait(bar, parity)) {
+    if (clock64() - t0 > HSTD_MBAR_TIMEOUT_CYCLES) {
+      printf("mbarrier watchdog: block (%d,%d,%d) thread %d waited > 2 s on smem barrier 0x%x parity %u\n", blockIdx.x,
+             blockIdx.y, blockIdx.z, threadIdx.x, smem_u32(bar), parity);
+      __trap();
+    }
+  }
+#else
   while (!mbar_try_wait(bar, parity)) {
   }
+#endif
 }
 
 // ---------------------------------------------------------------- TMA

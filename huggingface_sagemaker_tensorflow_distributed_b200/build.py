@@ -73,9 +73,13 @@ def _compile_one(nvcc: str, src: Path, verbose: bool) -> tuple[Path, str]:
     return obj, proc.stderr
 
 
-def build(force: bool = False, verbose: bool = False) -> Path:
-    """Compile every csrc/*.cu for sm_100a and link libhstd_b200.so.  Returns its path."""
+def build(force: bool = False, verbose: bool = False, watchdog: bool = False) -> Path:
+    """Compile every csrc/*.cu for sm_100a and link libhstd_b200.so.  Returns its path.
+    ``watchdog=True`` (development) compiles the mbarrier waits with a 2-second trap, so a barrier
+    protocol bug fails a test instead of hanging the GPU."""
     nvcc = find_nvcc()
+    if watchdog and "-DHSTD_MBAR_WATCHDOG" not in NVCC_FLAGS:
+        NVCC_FLAGS.append("-DHSTD_MBAR_WATCHDOG")
     BUILD_DIR.mkdir(exist_ok=True)
     LIB_PATH.parent.mkdir(exist_ok=True)
     if force:
@@ -106,8 +110,9 @@ def main() -> None:
     ap = argparse.ArgumentParser()
     ap.add_argument("--force", action="store_true")
     ap.add_argument("--verbose", action="store_true")
+    ap.add_argument("--watchdog", action="store_true", help="development: trap when an mbarrier wait exceeds ~2 s")
     a = ap.parse_args()
-    print(build(force=a.force, verbose=a.verbose))
+    print(build(force=a.force, verbose=a.verbose, watchdog=a.watchdog))
 
 
 if __name__ == "__main__":
