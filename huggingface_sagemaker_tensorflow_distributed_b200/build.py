@@ -42,9 +42,15 @@ def find_nvcc() -> str:
     raise RuntimeError("nvcc not found (set NVCC=/path/to/nvcc)")
 
 
+EXPERIMENTAL = False  # --experimental: also link csrc/experimental/*.cu (kernels that have not been validated on a GPU)
+
+
 def _sources() -> list[Path]:
     # *.cu: sm_100a kernels; *.cpp: the host runtime (tokenizer, bucket manager, batch loader)
-    return sorted(list(CSRC.glob("*.cu")) + list(CSRC.glob("*.cpp")))
+    srcs = list(CSRC.glob("*.cu")) + list(CSRC.glob("*.cpp"))
+    if EXPERIMENTAL:
+        srcs += list((CSRC / "experimental").glob("*.cu"))
+    return sorted(srcs)
 
 
 def _digest(src: Path) -> str:
@@ -73,10 +79,12 @@ def _compile_one(nvcc: str, src: Path, verbose: bool) -> tuple[Path, str]:
     return obj, proc.stderr
 
 
-def build(force: bool = False, verbose: bool = False, watchdog: bool = False) -> Path:
+def build(force: bool = False, verbose: bool = False, watchdog: bool = False, experimental: bool = False) -> Path:
     """Compile every csrc/*.cu for sm_100a and link libhstd_b200.so.  Returns its path.
     ``watchdog=True`` (development) compiles the mbarrier waits with a 2-second trap, so a barrier
     protocol bug fails a test instead of hanging the GPU."""
+    global EXPERIMENTAL
+    EXPERIMENTAL = experimental
     nvcc = find_nvcc()
     if watchdog and "-DHSTD_MBAR_WATCHDOG" not in NVCC_FLAGS:
         NVCC_FLAGS.append("-DHSTD_MBAR_WATCHDOG")
@@ -95,12 +103,16 @@ def build(force: bool = False, verbose: bool = False, watchdog: bool = False) ->
             objs.append(obj)
             logs.append(log)
     newest = max(o.stat().st_mtime for o in objs)
-    if force or not LIB_PATH.exists() or LIB_PATH.stat().st_mtime < newest:
+    link_stamp = BUILD_DIR / "link.stamp"  # the set of objects + flags the current .so was linked from
+    link_sig = " ".join(sorted(o.name for o in objs)) + " | " + " ".join(NVCC_FLAGS)
+    relink = not link_stamp.exists() or link_stamp.read_text() != link_sig
+    if force or relink or not LIB_PATH.exists() or LIB_PATH.stat().st_mtime < newest:
         cmd = [nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", str(LIB_PATH), *map(str, objs),
                "-lpthread", "-ldl"]
         proc = subprocess.run(cmd, capture_output=True, text=True)
         if proc.returncode != 0:
             raise RuntimeError(f"link failed:\n{proc.stdout}\n{proc.stderr}")
+        link_stamp.write_text(link_sig)
     if verbose:
         sys.stderr.write("\n".join(l for l in logs if l))
     return LIB_PATH
@@ -111,8 +123,9 @@ def main() -> None:
     ap.add_argument("--force", action="store_true")
     ap.add_argument("--verbose", action="store_true")
     ap.add_argument("--watchdog", action="store_true", help="development: trap when an mbarrier wait exceeds ~2 s")
+    ap.add_argument("--experimental", action="store_true", help="also link csrc/experimental/*.cu (not GPU-validated)")
     a = ap.parse_args()
-    print(build(force=a.force, verbose=a.verbose, watchdog=a.watchdog))
+    print(build(force=a.force, verbose=a.verbose, watchdog=a.watchdog, experimental=a.experimental))
 
 
 if __name__ == "__main__":
