@@ -24,7 +24,7 @@ from __future__ import annotations
 import os
 
 import math
-from dataclasses import dataclass, field
+from dataclasses import dataclass
 from typing import Callable, Dict, List, Optional, Tuple
 
 import torch

@@ -17,7 +17,7 @@ bf16→fp32 cast + Keras-AdamW + bf16 weight write-back are one kernel per bucke
 from __future__ import annotations
 
 from dataclasses import dataclass
-from typing import Dict, List, Optional, Tuple
+from typing import Dict, List, Tuple
 
 import torch
 import torch.distributed as dist

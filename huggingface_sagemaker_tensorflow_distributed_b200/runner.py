@@ -9,7 +9,6 @@ from __future__ import annotations
 
 import os
 import time
-from typing import Optional
 
 from . import trainer as T
 from .config import TrainConfig

@@ -1,6 +1,5 @@
 """Fused tcgen05 attention vs a PyTorch fp32 statement of the same op (and vs the unfused
 softmax kernel for the dropout mask)."""
-import math
 
 import pytest
 import torch

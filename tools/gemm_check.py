@@ -1,5 +1,4 @@
 """GEMM correctness + speed sweep (run on the B200 box).  Writes gpurun_out/gemm_check.txt."""
-import itertools
 import os
 import sys
 import time
