@@ -78,6 +78,9 @@ int get_tmap(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1, uint64
   if (r != CUDA_SUCCESS) return set_error(-4, "cuTensorMapEncodeTiled failed (code " + std::to_string(int(r)) + ")");
   {
     std::lock_guard<std::mutex> g(mu);
+    // a training job touches a few hundred distinct (pointer, shape) pairs; callers that stream fresh
+    // tensors through the C ABI must not grow the table without bound (128 B per entry)
+    if (cache.size() >= 8192) cache.clear();
     cache.emplace(key, m);
   }
   *out = m;
