@@ -49,6 +49,16 @@ struct ArKernelParams {
   int flag_slot;  // first flag slot of this bucket: flags[(flag_slot + block) * AR_MAX_WORLD + rank]
   int mode;       // hstd_ar_mode
   float inv_world;
+  // Row-sparse buckets (the embedding tables): the bucket is a stack of rows of `row_elems` elements and
+  // `row_stamp[row] == stamp` marks the rows that received a gradient on ANY rank in this step.
+  const uint32_t* row_stamp;
+  int row_elems;
+  int64_t row_vec0;  // bucket-relative index of the first 8-element vector of [start, start+numel)
+  // sparse-row marking kernel only
+  const int32_t* ids_peers[AR_MAX_WORLD];      // this step's token ids of every rank
+  int n_ids;                                   // ids per rank
+  int dense_rows;                              // leading rows of the bucket that are always live
+  int vocab_rows;                              // rows that ids may address (after the dense ones)
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -84,13 +94,15 @@ __device__ __forceinline__ void multimem_st_16B(void* mc, const uint4& v) {
                : "memory");
 }
 
-// All ranks' block `blockIdx.x` meet here.  Threads 0..world-1 each signal one peer and wait
-// for it.  `val` is monotonically increasing per (bucket, block).
-__device__ __forceinline__ void block_barrier(const ArKernelParams& p, uint32_t val) {
+// All ranks' block `block` meet here.  Threads 0..world-1 each signal one peer and wait for it.
+// `val` is monotonically increasing per (bucket, block).  Returns false when a peer never arrived
+// (the watchdog has then set the error word): the caller must not touch shared state any more.
+__device__ __forceinline__ bool block_barrier(const ArKernelParams& p, int block, uint32_t val) {
   __syncthreads();
+  int failed = 0;
   if (threadIdx.x < p.world) {
     const int peer = threadIdx.x;
-    const int64_t slot = int64_t(p.flag_slot + blockIdx.x) * AR_MAX_WORLD;
+    const int64_t slot = int64_t(p.flag_slot + block) * AR_MAX_WORLD;
     __threadfence_system();
     st_release_sys(p.flag_peers[peer] + slot + p.rank, val);
     const uint32_t* mine = p.flag_peers[p.rank] + slot + peer;
@@ -98,11 +110,17 @@ __device__ __forceinline__ void block_barrier(const ArKernelParams& p, uint32_t 
     while (int32_t(ld_acquire_sys(mine) - val) < 0) {
       if (clock64() - t0 > AR_TIMEOUT_CYCLES) {
         atomicExch(p.error, 1u + uint32_t(peer));
+        failed = 1;
         break;
       }
     }
   }
-  __syncthreads();
+  return __syncthreads_or(failed) == 0;
+}
+// Once the watchdog has fired on this rank every later bucket kernel leaves at once (instead of
+// waiting another ~10 s per bucket per step) until the host notices the error word.
+__device__ __forceinline__ bool already_failed(const ArKernelParams& p) {
+  return *reinterpret_cast<volatile const uint32_t*>(p.error) != 0u;
 }
 
 __device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
@@ -130,25 +148,50 @@ __device__ __forceinline__ uint4 adam8(const AdamScalars& sc, const ArKernelPara
   return pack8(w);
 }
 
-// MODE: 0 two-shot, 1 one-shot, 2 NVLS.  UPDATE: fused AdamW (true) or plain averaged
-// all-reduce written back into every rank's gradient arena (false; used by the bandwidth
-// sweep and the collective tests).
-template <int WORLD, int MODE, bool UPDATE>
-__global__ void __launch_bounds__(AR_THREADS) fused_allreduce_kernel(const ArKernelParams p) {
-  const uint32_t e = p.epoch[blockIdx.x];
-  block_barrier(p, 2 * e + 1);  // every rank's gradients of this bucket are complete
+// Row filter of a launch over a row-sparse bucket.
+//   ROWS_ALL      : dense bucket, every vector is reduced and updated.
+//   ROWS_LIVE     : only rows stamped in this step (some rank produced a gradient for them).
+//   ROWS_IDLE     : only rows NOT stamped: their gradient is exactly zero on every rank, so nothing is
+//                   read from any peer and no rank has to be waited for — m and v decay, the weight takes
+//                   its (history-driven) Adam step, the new bf16 row goes to every rank.  No rank reads an
+//                   idle embedding row during the step, so this part runs under the forward pass.
+enum { ROWS_ALL = 0, ROWS_LIVE = 1, ROWS_IDLE = 2 };
 
+// The work of one block of one rank.  `block` / `nblocks` are passed in (not blockIdx / gridDim) so the
+// single-GPU emulation below can run several ranks inside one cooperative grid.
+// MODE: 0 two-shot, 1 one-shot, 2 NVLS.  UPDATE: fused AdamW (true) or plain averaged all-reduce written
+// back into every rank's gradient arena (false; used by the bandwidth sweep and the collective tests).
+template <int WORLD, int MODE, bool UPDATE, int ROWS>
+__device__ __forceinline__ void allreduce_block(const ArKernelParams& p, int block, int nblocks) {
+  if (already_failed(p)) return;
+  const uint32_t e = p.epoch[block];
+  if (ROWS != ROWS_IDLE) {
+    // every rank's gradients of this bucket are complete
+    if (!block_barrier(p, block, 2 * e + 1)) return;  // a peer is gone: leave weights and optimizer state alone
+  }
   AdamScalars sc;
-  if (UPDATE) sc = load_adam_scalars(p.st);
+  uint32_t stamp = 0;
+  if (UPDATE) {
+    sc = load_adam_scalars(p.st);
+    stamp = uint32_t(p.st->step);
+  }
   const int64_t nvec_total = p.numel / 8;
   const int64_t nvec = MODE == 1 ? nvec_total : nvec_total / WORLD;     // vectors this rank reduces
   const int64_t first = MODE == 1 ? 0 : int64_t(p.rank) * nvec;         // first vector (bucket-relative)
-  const int64_t stride = int64_t(gridDim.x) * blockDim.x;
+  const int64_t stride = int64_t(nblocks) * blockDim.x;
+  const uint32_t row_vecs = ROWS != ROWS_ALL ? uint32_t(p.row_elems) / 8u : 1u;
 
-  for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < nvec; i += stride) {
+  for (int64_t i = block * int64_t(blockDim.x) + threadIdx.x; i < nvec; i += stride) {
+    if (ROWS != ROWS_ALL) {
+      const bool live = p.row_stamp[uint32_t(p.row_vec0 + first + i) / row_vecs] == stamp;
+      if (live != (ROWS == ROWS_LIVE)) continue;
+    }
     const int64_t elem = p.start + (first + i) * 8;  // arena element offset
     float g[8];
-    if (MODE == 2) {
+    if (ROWS == ROWS_IDLE) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) g[j] = 0.f;
+    } else if (MODE == 2) {
       unpack8(multimem_ld_reduce_bf16x8(p.g_mc + elem), g);
     } else {
       uint4 raw[WORLD];
@@ -193,8 +236,88 @@ __global__ void __launch_bounds__(AR_THREADS) fused_allreduce_kernel(const ArKer
     }
   }
 
-  block_barrier(p, 2 * e + 2);  // all peers finished reading our gradients / writing our weights
-  if (threadIdx.x == 0) p.epoch[blockIdx.x] = e + 1;
+  if (ROWS != ROWS_IDLE) {
+    block_barrier(p, block, 2 * e + 2);  // all peers finished reading our gradients / writing our weights
+    if (threadIdx.x == 0) p.epoch[block] = e + 1;
+  }
+}
+
+template <int WORLD, int MODE, bool UPDATE, int ROWS>
+__global__ void __launch_bounds__(AR_THREADS) fused_allreduce_kernel(const ArKernelParams p) {
+  allreduce_block<WORLD, MODE, UPDATE, ROWS>(p, blockIdx.x, gridDim.x);
+}
+
+// Single-GPU emulation of a WORLD-rank launch, for tests and profiling on a box with fewer GPUs than
+// ranks: ONE cooperative grid of WORLD x blocks CTAs (co-residency is what lets the flag barriers
+// complete), rank = blockIdx.x / blocks, every "peer" arena lives on this device.  Runs the very same
+// per-block code as the real kernel.  NVLS needs a multicast mapping and cannot be emulated.
+struct ArEmuParams {
+  ArKernelParams base;
+  float* master[AR_MAX_WORLD]; float* m[AR_MAX_WORLD]; float* v[AR_MAX_WORLD];
+  uint32_t* epoch[AR_MAX_WORLD];
+  uint32_t* error[AR_MAX_WORLD];
+  int blocks;
+};
+template <int WORLD, int MODE, bool UPDATE, int ROWS>
+__global__ void __launch_bounds__(AR_THREADS) fused_allreduce_emulated_kernel(const __grid_constant__ ArEmuParams ep) {
+  const int rank = blockIdx.x / ep.blocks, block = blockIdx.x % ep.blocks;
+  ArKernelParams p = ep.base;
+  p.rank = rank;
+  p.master = ep.master[rank]; p.m = ep.m[rank]; p.v = ep.v[rank];
+  p.epoch = ep.epoch[rank];
+  p.error = ep.error[rank];
+  allreduce_block<WORLD, MODE, UPDATE, ROWS>(p, block, ep.blocks);
+}
+
+// Start of a step, row-sparse bucket: learn which embedding rows ANY rank will produce a gradient for.
+// The token ids are inputs, so this is known long before backward: every rank reads every rank's ids
+// (peer loads, a few KB), stamps the rows with the current step number and clears those rows of its own
+// gradient arena (the scatter-add of the embedding backward accumulates into them; rows nobody stamps are
+// never read, so the 47 MB table is never zeroed or reduced densely).  The leading `dense_rows` rows of the
+// bucket (LayerNorm, position and token-type tables) are always live.
+__device__ __forceinline__ void mark_rows_block(const ArKernelParams& p, int block, int nblocks) {
+  if (already_failed(p)) return;
+  const uint32_t e = p.epoch[block];
+  // every rank has staged this step's ids (the host-to-device copy precedes this kernel in stream order)
+  if (!block_barrier(p, block, 2 * e + 1)) return;
+  const uint32_t stamp = uint32_t(p.st->step);
+  uint32_t* stamps = const_cast<uint32_t*>(p.row_stamp);
+  for (int r = block * blockDim.x + threadIdx.x; r < p.dense_rows; r += nblocks * blockDim.x) stamps[r] = stamp;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, warps = blockDim.x >> 5;
+  const int total = p.world * p.n_ids;
+  const int row_vecs = p.row_elems / 8;
+  for (int t = block * warps + warp; t < total; t += nblocks * warps) {
+    const int src = t / p.n_ids, k = t - src * p.n_ids;
+    int id = 0;
+    uint32_t old = stamp;
+    if (lane == 0) {
+      id = p.ids_peers[src][k];  // relaxed peer load; ordered after the barrier's acquire
+      if (id >= 0 && id < p.vocab_rows) old = atomicExch(stamps + p.dense_rows + id, stamp);
+    }
+    id = __shfl_sync(0xffffffffu, id, 0);
+    old = __shfl_sync(0xffffffffu, old, 0);
+    if (old == stamp) continue;  // somebody else got here first (or the id is out of range)
+    uint4* row = reinterpret_cast<uint4*>(const_cast<__nv_bfloat16*>(p.g_peers[p.rank]) + p.start +
+                                          int64_t(p.dense_rows + id) * p.row_elems);
+    for (int c = lane; c < row_vecs; c += 32) row[c] = make_uint4(0, 0, 0, 0);
+  }
+  // peers have finished reading our ids: the host may stage the next step's batch once this step is over
+  block_barrier(p, block, 2 * e + 2);
+  if (threadIdx.x == 0) p.epoch[block] = e + 1;
+}
+__global__ void __launch_bounds__(AR_THREADS) mark_rows_kernel(const ArKernelParams p) {
+  mark_rows_block(p, blockIdx.x, gridDim.x);
+}
+__global__ void __launch_bounds__(AR_THREADS) mark_rows_emulated_kernel(const __grid_constant__ ArEmuParams ep) {
+  const int rank = blockIdx.x / ep.blocks, block = blockIdx.x % ep.blocks;
+  ArKernelParams p = ep.base;
+  p.rank = rank;
+  p.epoch = ep.epoch[rank];
+  p.error = ep.error[rank];
+  // in the emulation every rank has its own stamp array and gradient arena; they are passed through the
+  // optimizer-state slots that this kernel does not otherwise use
+  p.row_stamp = reinterpret_cast<const uint32_t*>(ep.master[rank]);
+  mark_rows_block(p, block, ep.blocks);
 }
 
 // world == 1 or "my optimizer is local" case on IPC arenas: AdamW over owned vectors only.
@@ -209,15 +332,52 @@ __global__ void __launch_bounds__(AR_THREADS) local_update_kernel(const ArKernel
   }
 }
 
-template <int MODE, bool UPDATE>
+template <int MODE, bool UPDATE, int ROWS>
 static int launch_world(const ArKernelParams& p, int blocks, cudaStream_t s) {
   switch (p.world) {
-    case 2: fused_allreduce_kernel<2, MODE, UPDATE><<<blocks, AR_THREADS, 0, s>>>(p); break;
-    case 4: fused_allreduce_kernel<4, MODE, UPDATE><<<blocks, AR_THREADS, 0, s>>>(p); break;
-    case 8: fused_allreduce_kernel<8, MODE, UPDATE><<<blocks, AR_THREADS, 0, s>>>(p); break;
+    case 1:  // a rank on its own: the row-sparse optimizer without peers (timing aid, single-GPU sparse update)
+      if (MODE != 0 || !UPDATE) return set_error(-1, "allreduce: world 1 exists for the two-shot optimizer form only");
+      fused_allreduce_kernel<1, 0, true, ROWS><<<blocks, AR_THREADS, 0, s>>>(p);
+      break;
+    case 2: fused_allreduce_kernel<2, MODE, UPDATE, ROWS><<<blocks, AR_THREADS, 0, s>>>(p); break;
+    case 4: fused_allreduce_kernel<4, MODE, UPDATE, ROWS><<<blocks, AR_THREADS, 0, s>>>(p); break;
+    case 8: fused_allreduce_kernel<8, MODE, UPDATE, ROWS><<<blocks, AR_THREADS, 0, s>>>(p); break;
     default: return set_error(-1, "allreduce: world size must be 2, 4 or 8");
   }
   return check_launch("fused_allreduce");
+}
+template <int MODE, bool UPDATE>
+static int launch_rows(const ArKernelParams& p, int rows, int blocks, cudaStream_t s) {
+  switch (rows) {
+    case ROWS_ALL: return launch_world<MODE, UPDATE, ROWS_ALL>(p, blocks, s);
+    case ROWS_LIVE: return launch_world<MODE, UPDATE, ROWS_LIVE>(p, blocks, s);
+    case ROWS_IDLE: return launch_world<MODE, UPDATE, ROWS_IDLE>(p, blocks, s);
+    default: return set_error(-1, "allreduce: unknown row filter");
+  }
+}
+
+template <typename Kern>
+static int launch_cooperative(Kern kern, const ArEmuParams& ep, int world, cudaStream_t s) {
+  int per_sm = 0, dev = 0, sms = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, AR_THREADS, 0);
+  if (world * ep.blocks > per_sm * sms)
+    return set_error(-1, "allreduce emulation: world x blocks CTAs cannot be co-resident on this GPU");
+  void* args[] = {const_cast<ArEmuParams*>(&ep)};
+  cudaError_t e = cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(kern), dim3(world * ep.blocks),
+                                              dim3(AR_THREADS), args, 0, s);
+  if (e != cudaSuccess) return set_error(-6, std::string("allreduce emulation: ") + cudaGetErrorString(e));
+  return 0;
+}
+template <int MODE, bool UPDATE, int ROWS>
+static int launch_emulated_world(const ArEmuParams& ep, cudaStream_t s) {
+  switch (ep.base.world) {
+    case 2: return launch_cooperative(fused_allreduce_emulated_kernel<2, MODE, UPDATE, ROWS>, ep, 2, s);
+    case 4: return launch_cooperative(fused_allreduce_emulated_kernel<4, MODE, UPDATE, ROWS>, ep, 4, s);
+    case 8: return launch_cooperative(fused_allreduce_emulated_kernel<8, MODE, UPDATE, ROWS>, ep, 8, s);
+    default: return set_error(-1, "allreduce: world size must be 2, 4 or 8");
+  }
 }
 
 }  // namespace hstd
@@ -229,17 +389,13 @@ extern "C" HSTD_API int64_t hstd_allreduce_flag_words(int num_buckets) {
   return int64_t(num_buckets) * AR_MAX_BLOCKS * AR_MAX_WORLD;
 }
 
-extern "C" HSTD_API int hstd_fused_allreduce(const hstd_allreduce_args* a, void* stream) {
+static int fill_params(const hstd_allreduce_args* a, ArKernelParams& p) {
   if (a->world < 1 || a->world > AR_MAX_WORLD) return set_error(-1, "allreduce: bad world size");
-  const bool local_only = a->mode == HSTD_AR_LOCAL || a->world == 1;
-  if (a->numel % (local_only ? 8 : 8 * a->world) != 0)
-    return set_error(-1, "allreduce: bucket size must be a multiple of 8*world (8 for the local update)");
-  if (a->start % 8 != 0) return set_error(-1, "allreduce: bucket start must be a multiple of 8");
-  ArKernelParams p;
   for (int r = 0; r < AR_MAX_WORLD; ++r) {
     p.g_peers[r] = r < a->world ? static_cast<const __nv_bfloat16*>(a->g_peers[r]) : nullptr;
     p.w_peers[r] = r < a->world ? static_cast<__nv_bfloat16*>(a->w_peers[r]) : nullptr;
     p.flag_peers[r] = r < a->world ? static_cast<uint32_t*>(a->flag_peers[r]) : nullptr;
+    p.ids_peers[r] = r < a->world ? static_cast<const int32_t*>(a->ids_peers[r]) : nullptr;
   }
   p.g_mc = static_cast<const __nv_bfloat16*>(a->g_mc);
   p.w_mc = static_cast<__nv_bfloat16*>(a->w_mc);
@@ -252,11 +408,41 @@ extern "C" HSTD_API int hstd_fused_allreduce(const hstd_allreduce_args* a, void*
   p.flag_slot = a->bucket_index * AR_MAX_BLOCKS;
   p.mode = a->mode;
   p.inv_world = 1.0f / float(a->world);
+  p.row_stamp = static_cast<const uint32_t*>(a->row_stamp);
+  p.row_elems = a->row_elems;
+  p.row_vec0 = a->row_elem0 / 8;
+  p.n_ids = a->n_ids; p.dense_rows = a->dense_rows; p.vocab_rows = a->vocab_rows;
+  return 0;
+}
+
+static int check_rows(const hstd_allreduce_args* a) {
+  if (a->rows == HSTD_AR_ROWS_ALL) return 0;
+  if (a->rows != HSTD_AR_ROWS_LIVE && a->rows != HSTD_AR_ROWS_IDLE) return set_error(-1, "allreduce: unknown row filter");
+  if (!a->update) return set_error(-1, "allreduce: row filters exist for the fused optimizer form only");
+  if (!a->row_stamp || a->row_elems <= 0 || a->row_elems % 8 != 0)
+    return set_error(-1, "allreduce: row filter needs row_stamp and row_elems (multiple of 8)");
+  if (a->numel % a->row_elems != 0) return set_error(-1, "allreduce: a row-sparse bucket must be whole rows");
+  if (a->mode == HSTD_AR_ONE_SHOT) return set_error(-1, "allreduce: row filters need the sharded (two-shot / NVLS) form");
+  return 0;
+}
+
+static int clamp_blocks(int blocks) {
+  if (blocks <= 0) blocks = 64;
+  return blocks > AR_MAX_BLOCKS ? AR_MAX_BLOCKS : blocks;
+}
+
+extern "C" HSTD_API int hstd_fused_allreduce(const hstd_allreduce_args* a, void* stream) {
+  ArKernelParams p;
+  if (int rc = fill_params(a, p)) return rc;
+  const bool local_only = a->mode == HSTD_AR_LOCAL || (a->world == 1 && a->rows == HSTD_AR_ROWS_ALL);
+  if (a->row_elem0 % 8 != 0) return set_error(-1, "allreduce: row_elem0 must be a multiple of 8");
+  if (a->numel % (local_only ? 8 : 8 * a->world) != 0)
+    return set_error(-1, "allreduce: bucket size must be a multiple of 8*world (8 for the local update)");
+  if (a->start % 8 != 0) return set_error(-1, "allreduce: bucket start must be a multiple of 8");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  int blocks = a->blocks > 0 ? a->blocks : 64;
-  if (blocks > AR_MAX_BLOCKS) blocks = AR_MAX_BLOCKS;
+  int blocks = clamp_blocks(a->blocks);
   const bool update = a->update != 0;
-  if (a->mode == HSTD_AR_LOCAL || a->world == 1) {
+  if (local_only) {
     if (!update) return 0;
     const int64_t nvec = a->numel / 8;
     int64_t need = (nvec + AR_THREADS - 1) / AR_THREADS;
@@ -266,12 +452,77 @@ extern "C" HSTD_API int hstd_fused_allreduce(const hstd_allreduce_args* a, void*
   }
   if (update && (!a->master || !a->m || !a->v || !a->state)) return set_error(-1, "allreduce: optimizer state missing");
   if (a->mode == HSTD_AR_NVLS && (!a->g_mc || !a->w_mc)) return set_error(-1, "allreduce: NVLS needs multicast pointers");
+  if (int rc = check_rows(a)) return rc;
   switch (a->mode) {
-    case HSTD_AR_TWO_SHOT: return update ? launch_world<0, true>(p, blocks, s) : launch_world<0, false>(p, blocks, s);
-    case HSTD_AR_ONE_SHOT: return update ? launch_world<1, true>(p, blocks, s) : launch_world<1, false>(p, blocks, s);
-    case HSTD_AR_NVLS: return update ? launch_world<2, true>(p, blocks, s) : launch_world<2, false>(p, blocks, s);
+    case HSTD_AR_TWO_SHOT:
+      return update ? launch_rows<0, true>(p, a->rows, blocks, s) : launch_world<0, false, ROWS_ALL>(p, blocks, s);
+    case HSTD_AR_ONE_SHOT:
+      return update ? launch_world<1, true, ROWS_ALL>(p, blocks, s) : launch_world<1, false, ROWS_ALL>(p, blocks, s);
+    case HSTD_AR_NVLS:
+      return update ? launch_rows<2, true>(p, a->rows, blocks, s) : launch_world<2, false, ROWS_ALL>(p, blocks, s);
     default: return set_error(-1, "allreduce: unknown mode");
   }
+}
+
+extern "C" HSTD_API int hstd_sparse_rows_mark(const hstd_allreduce_args* a, void* stream) {
+  ArKernelParams p;
+  if (int rc = fill_params(a, p)) return rc;
+  if (!a->row_stamp || !a->state || a->row_elems <= 0 || a->row_elems % 8 != 0 || a->n_ids <= 0 || a->dense_rows < 0 ||
+      a->vocab_rows <= 0)
+    return set_error(-1, "sparse_rows_mark: row_stamp, state, row_elems (multiple of 8), n_ids, vocab_rows required");
+  for (int r = 0; r < a->world; ++r)
+    if (!a->ids_peers[r]) return set_error(-1, "sparse_rows_mark: ids pointer of every rank required");
+  mark_rows_kernel<<<clamp_blocks(a->blocks), AR_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(p);
+  return check_launch("sparse_rows_mark");
+}
+
+// ------------------------------------------------------------------ single-GPU emulation (tests, profiling)
+static int fill_emu(const hstd_allreduce_args* per_rank, int world, ArEmuParams& ep) {
+  if (world != 2 && world != 4 && world != 8) return set_error(-1, "allreduce emulation: world must be 2, 4 or 8");
+  if (int rc = fill_params(&per_rank[0], ep.base)) return rc;
+  ep.base.world = world;
+  ep.base.inv_world = 1.0f / float(world);
+  for (int r = 0; r < world; ++r) {
+    const hstd_allreduce_args& a = per_rank[r];
+    if (a.start != per_rank[0].start || a.numel != per_rank[0].numel || a.mode != per_rank[0].mode ||
+        a.bucket_index != per_rank[0].bucket_index)
+      return set_error(-1, "allreduce emulation: every rank must describe the same bucket");
+    ep.master[r] = a.master; ep.m[r] = a.m; ep.v[r] = a.v;
+    ep.epoch[r] = static_cast<uint32_t*>(a.epoch);
+    ep.error[r] = static_cast<uint32_t*>(a.error);
+  }
+  ep.blocks = clamp_blocks(per_rank[0].blocks);
+  return 0;
+}
+
+extern "C" HSTD_API int hstd_fused_allreduce_emulated(const hstd_allreduce_args* per_rank, int world, void* stream) {
+  ArEmuParams ep;
+  if (int rc = fill_emu(per_rank, world, ep)) return rc;
+  const hstd_allreduce_args& a = per_rank[0];
+  if (a.numel % (8 * world) != 0 || a.start % 8 != 0) return set_error(-1, "allreduce emulation: bad bucket bounds");
+  if (int rc = check_rows(&a)) return rc;
+  const bool update = a.update != 0;
+  if (update && !a.state) return set_error(-1, "allreduce emulation: step state missing");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (a.mode == HSTD_AR_TWO_SHOT) {
+    if (!update) return launch_emulated_world<0, false, ROWS_ALL>(ep, s);
+    switch (a.rows) {
+      case HSTD_AR_ROWS_LIVE: return launch_emulated_world<0, true, ROWS_LIVE>(ep, s);
+      case HSTD_AR_ROWS_IDLE: return launch_emulated_world<0, true, ROWS_IDLE>(ep, s);
+      default: return launch_emulated_world<0, true, ROWS_ALL>(ep, s);
+    }
+  }
+  if (a.mode == HSTD_AR_ONE_SHOT)
+    return update ? launch_emulated_world<1, true, ROWS_ALL>(ep, s) : launch_emulated_world<1, false, ROWS_ALL>(ep, s);
+  return set_error(-1, "allreduce emulation: two-shot and one-shot only (NVLS needs a multicast mapping)");
+}
+
+// per_rank[r].master carries rank r's row_stamp array here (each emulated rank keeps its own).
+extern "C" HSTD_API int hstd_sparse_rows_mark_emulated(const hstd_allreduce_args* per_rank, int world, void* stream) {
+  ArEmuParams ep;
+  if (int rc = fill_emu(per_rank, world, ep)) return rc;
+  for (int r = 0; r < world; ++r) ep.master[r] = reinterpret_cast<float*>(per_rank[r].row_stamp);
+  return launch_cooperative(mark_rows_emulated_kernel, ep, world, static_cast<cudaStream_t>(stream));
 }
 
 // ------------------------------------------------------------------ IPC plumbing (C++ side of N4)
@@ -299,19 +550,4 @@ extern "C" HSTD_API int hstd_ipc_close(void* ptr) {
 extern "C" HSTD_API int hstd_ipc_free(void* ptr) {
   cudaError_t e = cudaFree(ptr);
   return e == cudaSuccess ? 0 : set_error(-7, std::string("ipc_free: ") + cudaGetErrorString(e));
-}
-// Same-process multi-GPU (MirroredStrategy front-end): plain peer access, no IPC handles.
-extern "C" HSTD_API int hstd_enable_peer_access(int dev, int peer) {
-  int can = 0;
-  cudaDeviceCanAccessPeer(&can, dev, peer);
-  if (!can) return set_error(-7, "peer access not possible between these devices");
-  int cur = 0;
-  cudaGetDevice(&cur);
-  cudaSetDevice(dev);
-  cudaError_t e = cudaDeviceEnablePeerAccess(peer, 0);
-  cudaSetDevice(cur);
-  if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled)
-    return set_error(-7, std::string("enable_peer_access: ") + cudaGetErrorString(e));
-  cudaGetLastError();
-  return 0;
 }

@@ -40,8 +40,11 @@ struct hstd_loader {
     std::thread worker;
 
     void fill(int slot, int b) {
-        const int64_t lo = static_cast<int64_t>(b) * batch;
-        const int64_t hi = std::min<int64_t>(lo + batch, static_cast<int64_t>(indices.size()));
+        // batches past the end of this rank's shard are all padding (ranks whose shard is one sample
+        // shorter still take the common number of steps)
+        const int64_t n_idx = static_cast<int64_t>(indices.size());
+        const int64_t lo = std::min<int64_t>(static_cast<int64_t>(b) * batch, n_idx);
+        const int64_t hi = std::min<int64_t>(lo + batch, n_idx);
         const size_t row_bytes = sizeof(int32_t) * static_cast<size_t>(seq_len);
         int32_t* oi = slot_ids[slot];
         int32_t* om = slot_mask[slot];
@@ -114,7 +117,7 @@ extern "C" HSTD_API hstd_loader* hstd_loader_create(const int32_t* ids, const in
         return nullptr;
     }
     const int64_t max_batches = (n_indices + batch - 1) / batch;
-    if (num_batches < 0 || num_batches > max_batches) num_batches = static_cast<int>(max_batches);
+    if (num_batches < 0) num_batches = static_cast<int>(max_batches);
     for (int64_t i = 0; i < n_indices; ++i)
         if (indices[i] < 0 || indices[i] >= n_rows) {
             hstd::set_error(-1, "hstd_loader_create: index out of range");

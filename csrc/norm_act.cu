@@ -478,8 +478,18 @@ extern "C" HSTD_API int hstd_ln_bwd(const hstd_ln_bwd_args* a, void* stream) {
 
 extern "C" HSTD_API int64_t hstd_colsum_partials_floats(int N) { return int64_t(COLSUM_ROWGROUPS_WS) * N; }
 
+// The column-sum kernels read eight bf16 per 16-byte vector load: a raw-C caller handing in an
+// odd pointer or row stride would otherwise get a misaligned-address fault instead of an error.
+static int colsum_check_alignment(const void* x, int64_t ld, const char* who) {
+  if (reinterpret_cast<uintptr_t>(x) & 15u)
+    return set_error(-1, std::string(who) + ": x must be 16-byte aligned");
+  if (ld % 8 != 0) return set_error(-1, std::string(who) + ": ld must be a multiple of 8 elements (16 bytes)");
+  return 0;
+}
+
 extern "C" HSTD_API int hstd_colsum(const void* x, int64_t ld, int M, int N, void* out, float* partials, void* stream) {
   if (N % 8 != 0) return set_error(-1, "colsum: N must be a multiple of 8");
+  if (int rc = colsum_check_alignment(x, ld, "colsum")) return rc;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   dim3 grid((N + 255) / 256, COLSUM_ROWGROUPS_WS);
   launch_pdl(colsum_partial_kernel, grid, dim3(256), 0, s, static_cast<const __nv_bfloat16*>(x), ld, M, N, partials);
@@ -576,6 +586,7 @@ extern "C" HSTD_API int hstd_colsum_noalloc(const void* x, int64_t ld, int M, in
     return set_error(-1, "colsum_noalloc: N = " + std::to_string(N) + " exceeds the built-in scratch (max N = " +
                              std::to_string(COLSUM_NOALLOC_MAX_N) + "); use hstd_colsum with a caller workspace");
   if (M <= 0 || N <= 0) return set_error(-1, "colsum_noalloc: empty matrix");
+  if (int rc = colsum_check_alignment(x, ld, "colsum_noalloc")) return rc;
   float* scratch = nullptr;
   if (int rc = colsum_noalloc_scratch(&scratch)) return rc;
   cudaStream_t s = static_cast<cudaStream_t>(stream);

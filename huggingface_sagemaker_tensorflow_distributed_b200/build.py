@@ -42,15 +42,9 @@ def find_nvcc() -> str:
     raise RuntimeError("nvcc not found (set NVCC=/path/to/nvcc)")
 
 
-EXPERIMENTAL = False  # --experimental: also link csrc/experimental/*.cu (kernels that have not been validated on a GPU)
-
-
 def _sources() -> list[Path]:
     # *.cu: sm_100a kernels; *.cpp: the host runtime (tokenizer, bucket manager, batch loader)
-    srcs = list(CSRC.glob("*.cu")) + list(CSRC.glob("*.cpp"))
-    if EXPERIMENTAL:
-        srcs += list((CSRC / "experimental").glob("*.cu"))
-    return sorted(srcs)
+    return sorted(list(CSRC.glob("*.cu")) + list(CSRC.glob("*.cpp")))
 
 
 def _digest(src: Path) -> str:
@@ -79,12 +73,10 @@ def _compile_one(nvcc: str, src: Path, verbose: bool) -> tuple[Path, str]:
     return obj, proc.stderr
 
 
-def build(force: bool = False, verbose: bool = False, watchdog: bool = False, experimental: bool = False) -> Path:
+def build(force: bool = False, verbose: bool = False, watchdog: bool = False) -> Path:
     """Compile every csrc/*.cu for sm_100a and link libhstd_b200.so.  Returns its path.
     ``watchdog=True`` (development) compiles the mbarrier waits with a 2-second trap, so a barrier
     protocol bug fails a test instead of hanging the GPU."""
-    global EXPERIMENTAL
-    EXPERIMENTAL = experimental
     nvcc = find_nvcc()
     if watchdog and "-DHSTD_MBAR_WATCHDOG" not in NVCC_FLAGS:
         NVCC_FLAGS.append("-DHSTD_MBAR_WATCHDOG")
@@ -123,9 +115,8 @@ def main() -> None:
     ap.add_argument("--force", action="store_true")
     ap.add_argument("--verbose", action="store_true")
     ap.add_argument("--watchdog", action="store_true", help="development: trap when an mbarrier wait exceeds ~2 s")
-    ap.add_argument("--experimental", action="store_true", help="also link csrc/experimental/*.cu (not GPU-validated)")
     a = ap.parse_args()
-    print(build(force=a.force, verbose=a.verbose, watchdog=a.watchdog, experimental=a.experimental))
+    print(build(force=a.force, verbose=a.verbose, watchdog=a.watchdog))
 
 
 if __name__ == "__main__":

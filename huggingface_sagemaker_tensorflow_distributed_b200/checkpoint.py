@@ -64,4 +64,6 @@ def load_training_state(load_dir: str) -> Optional[dict]:
     p = os.path.join(load_dir, TRAINING_STATE_NAME)
     if not os.path.exists(p):
         return None
-    return torch.load(p, map_location="cpu", weights_only=False)
+    # tensors, ints and dicts only: the restricted unpickler is enough and a checkpoint directory from an
+    # untrusted source cannot run code through this path
+    return torch.load(p, map_location="cpu", weights_only=True)

@@ -169,14 +169,21 @@ class BatchedDataset:
         self.prefetch, self.num_slots = bool(prefetch), max(3, int(num_slots))
         self._loader = None
         idx = np.arange(len(ds))
+        # Every rank must take the same number of steps: the fused all-reduce is a collective, and a rank
+        # that runs one batch more than its peers would wait for them in the flag barrier.  With
+        # len(ds) % world != 0 the strided shards differ by one sample, so the batch count is derived
+        # from the LONGEST shard (DistributedSampler semantics); a rank that runs out of samples pads
+        # with rows labelled IGNORE_LABEL, which count towards neither loss nor accuracy.
+        self._common_len = len(idx)
         if shard and world_size > 1:
+            self._common_len = (len(idx) + world_size - 1) // world_size
             idx = idx[rank::world_size]
         self.indices = idx
         self.max_batches = max_batches
         self.pin_memory = pin_memory and torch.cuda.is_available()
 
     def __len__(self) -> int:
-        n = (len(self.indices) + self.batch_size - 1) // self.batch_size
+        n = (self._common_len + self.batch_size - 1) // self.batch_size
         return n if self.max_batches < 0 else min(n, self.max_batches)
 
     @property

@@ -277,6 +277,7 @@ class EngineBackend:
             plan.ops.append(run)
             plan.names.append(n + "@side")
         plan.side_dirty = True
+        plan.side_used = True  # the side stream is part of this plan's captured graph from here on
 
     def _join_side(self, plan) -> None:
         """Main stream waits for everything queued on the side stream so far."""
@@ -352,6 +353,10 @@ class EngineBackend:
         scale = 1.0 / math.sqrt(dh)
         i32 = torch.int32
         ids = self._buf(plan, "ids", (B, S), i32)
+        if train:
+            shared_ids = self.dp.ids_buffer(B * S)  # row-sparse embedding reduce: peers read this step's ids
+            if shared_ids is not None:
+                ids = plan.bufs["ids"] = shared_ids.view(B, S)
         mask = self._buf(plan, "mask", (B, S), i32)
         labels = self._buf(plan, "labels", (B,), i32)
         pos = self._buf(plan, "pos", (B, S), i32)
@@ -397,6 +402,7 @@ class EngineBackend:
             sch = self.sched
             op(lambda: K.step_prologue(st, sch.base_lr, sch.kind, sch.total_steps, sch.warmup_steps, o.beta_1, o.beta_2,
                                        o.epsilon, o.weight_decay))
+            self.dp.after_step_prologue(plan, B * S)
         op(lambda: K.position_ids(ids, pos, cfg.model_type == "roberta", cfg.pad_token_id))
         type0 = self.W("emb.tok_type.weight")[0] if cfg.type_vocab_size > 0 else None
 
@@ -480,7 +486,10 @@ class EngineBackend:
                              bias_grad=False)
             # FFN1: dW1, db1, dh1 = du·W1 + d(r2)
             self._linear_bwd(plan, du, h1[i], pfx + "ffn1", bufC, M, epilogue=G.EPI_ADD, aux=bufA, ldaux=d)
-            if self.dp.wants_early_buckets():
+            if self.dp.local_early_buckets() or dg is bufA:
+                # without hidden dropout (dg = bufA) the FFN2 weight-gradient GEMM on the side stream reads
+                # bufA, which the LN1 backward below overwrites (dpre = bufA).  (A distributed bucket released
+                # here does not need the join: its kernel waits for the side stream from the comm stream.)
                 self._join_side(plan)
             self.dp.after_grads(plan, [pfx + n for n in ("ln2.weight", "ln2.bias", "ffn2.weight", "ffn2.bias",
                                                           "ffn1.weight", "ffn1.bias")])
@@ -509,7 +518,12 @@ class EngineBackend:
                             dgamma=self.Gr("emb.ln.weight"), dbeta=self.Gr("emb.ln.bias"), partials=lnp, state=st,
                             p_out=p_hid, site_out=9000), 2)
         wg, pg = self.Gr("emb.word.weight"), self.Gr("emb.pos.weight")
-        op(lambda: (wg.zero_(), pg.zero_()), 2)
+        if self.dp.sparse_embedding():
+            # only the rows that are live in this step are ever read: the marking kernel cleared them long ago
+            op(lambda: pg.zero_(), 1)
+            self.dp.before_embedding_scatter(plan)
+        else:
+            op(lambda: (wg.zero_(), pg.zero_()), 2)
         op(lambda: K.embed_bwd(bufA, ids.view(-1), pos.view(-1), wg, pg))
         if cfg.type_vocab_size > 0:
             tg = self.Gr("emb.tok_type.weight")
@@ -605,6 +619,10 @@ class EngineBackend:
         plan = self._get_plan(B, S, train)
         names = plan.names + ["dp/optimizer"] * (len(plan.ops) - len(plan.names))
         return profile_ops(plan.ops, names, repeats)
+
+    def poll_health(self) -> None:
+        """Cheap (non-blocking) check of the all-reduce watchdog; raises if a peer went missing."""
+        self.dp.poll_errors()
 
     def finish(self) -> None:
         torch.cuda.synchronize()

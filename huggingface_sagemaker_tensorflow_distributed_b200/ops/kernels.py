@@ -1,8 +1,8 @@
 """ctypes front-ends of the non-GEMM kernels (csrc/norm_act.cu, head_loss.cu, optimizer.cu).
 
 Thin by design: the engine pre-allocates every buffer and calls these with raw tensors; the
-wrappers only marshal pointers.  Each has a PyTorch fp32 statement of the same math in
-``ops/reference_ops.py`` that the GPU tests compare against.
+wrappers only marshal pointers.  The GPU tests (tests/test_kernels_gpu.py, test_attention_gpu.py)
+compare each against a plain PyTorch fp32 statement of the same math written next to the test.
 """
 from __future__ import annotations
 

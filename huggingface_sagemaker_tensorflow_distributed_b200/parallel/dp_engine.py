@@ -32,12 +32,19 @@ class Bucket:
     start: int  # element offsets into the arenas
     end: int
     names: List[str]
+    # row-sparse bucket (the embedding tables): a stack of rows of `row_elems` elements, `dense_rows` always-live
+    # rows (LayerNorm / token-type / position tables) followed by `vocab_rows` word-embedding rows
+    sparse: bool = False
+    row_elems: int = 0
+    dense_rows: int = 0
+    vocab_rows: int = 0
 
     @property
     def numel(self) -> int:
         return self.end - self.start
 
 
+P2P_WORLD_SIZES = (2, 4, 8)
 HEAD_PARAMS = ("head.out.weight", "head.out.bias", "head.dense.weight", "head.dense.bias")
 
 
@@ -56,15 +63,47 @@ def plan_buckets(slots: Dict[str, "object"], order: List[str], bucket_elems: int
     return buckets
 
 
+def plan_buckets_with_embeddings(slots, order: List[str], bucket_elems: int, world: int, row_sparse: bool) -> List[Bucket]:
+    """Encoder + head parameters are bucketed greedily; the embedding block (LayerNorm, token-type, position and
+    word tables — the tail of the readiness order, complete only when backward ends) is one bucket of its
+    own.  With ``row_sparse`` it is reduced row-sparsely: all its tensors are stacks of hidden-size rows."""
+    emb = [n for n in order if n.startswith("emb.")]
+    rest = [n for n in order if not n.startswith("emb.")]
+    assert order[-len(emb):] == emb and emb[-1] == "emb.word.weight"
+    buckets = plan_buckets(slots, rest, bucket_elems, world)
+    word = slots["emb.word.weight"]
+    d = word.shape[1]
+    start, end = slots[emb[0]].offset, word.end
+    b = Bucket(len(buckets), start, end, emb)
+    contiguous_rows = all(slots[n].numel % d == 0 and slots[n].end - slots[n].offset == slots[n].numel for n in emb)
+    if row_sparse and contiguous_rows and (end - start) % (8 * world) == 0:
+        b.sparse, b.row_elems = True, d
+        b.dense_rows, b.vocab_rows = (word.offset - start) // d, word.shape[0]
+    buckets.append(b)
+    return buckets
+
+
 class DPEngine:
     def __init__(self, engine, bucket_mb: float = 32.0, mode: str = "p2p"):
         self.engine = engine
         self.device = engine.device
         self.world, self.rank = comm.size(), comm.rank()
         self.mode = mode if self.world > 1 else "local"
+        if self.mode == "p2p" and self.world not in P2P_WORLD_SIZES:
+            # the fused kernels are instantiated for 2, 4 and 8 ranks (csrc/allreduce_sm100.cu); a box with
+            # 3, 5, 6 or 7 visible GPUs still trains, on the library all-reduce + flat AdamW path
+            import warnings
+
+            warnings.warn(f"fused NVLink all-reduce supports world sizes {P2P_WORLD_SIZES}, got {self.world}: "
+                          "falling back to comm mode 'nccl'")
+            self.mode = "nccl"
         self.total = engine.total
         order = list(engine.slots.keys())
-        self.buckets = plan_buckets(engine.slots, order, int(bucket_mb * (1 << 20) / 2), self.world)
+        import os
+
+        row_sparse = self.mode == "p2p" and os.environ.get("HSTD_SPARSE_EMB", "1") != "0"
+        self.buckets = plan_buckets_with_embeddings(engine.slots, order, int(bucket_mb * (1 << 20) / 2), self.world,
+                                                    row_sparse)
         self.name_to_bucket = {n: b.index for b in self.buckets for n in b.names}
         from ..ops import host
 
@@ -108,6 +147,9 @@ class DPEngine:
         (distributed p2p) or, on a single GPU, the per-bucket AdamW on the optimizer stream."""
         return (self.p2p is not None and self.distributed) or self._local_overlap()
 
+    def local_early_buckets(self) -> bool:
+        return self._local_overlap()
+
     def _local_overlap(self) -> bool:
         # Measured on B200 (DistilBERT, 1 GPU): overlapping the per-bucket AdamW with backward is a
         # net loss (2.63 vs 2.56 ms/step) — its HBM traffic slows the concurrent GEMMs more than it
@@ -121,6 +163,10 @@ class DPEngine:
     def check_errors(self) -> None:
         if self.p2p is not None:
             self.p2p.check_errors()
+
+    def poll_errors(self) -> None:
+        if self.p2p is not None:
+            self.p2p.poll_errors()
 
     def describe(self) -> dict:
         d = {"mode": self.mode, "world": self.world, "num_buckets": len(self.buckets)}
@@ -177,6 +223,22 @@ class DPEngine:
         dist.broadcast(step_state, src=root)
 
     # ------------------------------------------------------------------ hooks used while recording a plan
+    def sparse_embedding(self) -> bool:
+        """True when the embedding bucket is reduced row-sparsely (distributed p2p training)."""
+        return self.p2p is not None and self.distributed and self.p2p.sparse is not None
+
+    def ids_buffer(self, n: int):
+        """Peer-visible slot for the step's token ids (row-sparse embedding reduce), else None."""
+        return self.p2p.ids_view(n) if self.sparse_embedding() else None
+
+    def after_step_prologue(self, plan, n_ids: int) -> None:
+        if self.sparse_embedding():
+            self.p2p.record_step_start(plan, self.engine.state, self.master, self.m, self.v, n_ids)
+
+    def before_embedding_scatter(self, plan) -> None:
+        if self.sparse_embedding():
+            self.p2p.record_wait_rows_marked(plan)
+
     def begin_backward(self, plan) -> None:
         self._tracker.reset()
         if self.p2p is not None and self.distributed:
@@ -187,9 +249,11 @@ class DPEngine:
         tracker releases buckets strictly in order because the arena is in readiness order."""
         ready = [self.buckets[i] for i in self._tracker.mark([self._param_index[n] for n in names])]
         if self.p2p is not None and self.distributed:
+            side = self.engine.side_stream if getattr(plan, "side_used", False) else None
             for b in ready:
                 self.p2p.record_bucket(plan, b, self.engine.state, self.master, self.m, self.v,
-                                       overlap=self.engine.overlap)
+                                       overlap=self.engine.overlap, side_stream=side,
+                                       last=b.index >= len(self.buckets) - 2)
         elif self._local_overlap():
             # single GPU: the HBM-bound AdamW of a finished bucket runs on its own stream under the
             # tensor-bound rest of backward instead of serially at the end of the step

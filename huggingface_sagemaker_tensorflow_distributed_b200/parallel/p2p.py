@@ -35,13 +35,25 @@ class AllreduceArgs(C.Structure):
                 ("g_mc", C.c_void_p), ("w_mc", C.c_void_p), ("epoch", C.c_void_p), ("error", C.c_void_p),
                 ("master", C.c_void_p), ("m", C.c_void_p), ("v", C.c_void_p), ("state", C.c_void_p),
                 ("start", C.c_int64), ("numel", C.c_int64), ("world", C.c_int32), ("rank", C.c_int32),
-                ("bucket_index", C.c_int32), ("mode", C.c_int32), ("update", C.c_int32), ("blocks", C.c_int32)]
+                ("bucket_index", C.c_int32), ("mode", C.c_int32), ("update", C.c_int32), ("blocks", C.c_int32),
+                ("row_stamp", C.c_void_p), ("ids_peers", C.c_void_p * 8), ("row_elems", C.c_int32),
+                ("rows", C.c_int32), ("n_ids", C.c_int32), ("dense_rows", C.c_int32), ("vocab_rows", C.c_int32),
+                ("reserved_", C.c_int32), ("row_elem0", C.c_int64)]
+
+
+ROWS_ALL, ROWS_LIVE, ROWS_IDLE = 0, 1, 2
+MAX_IDS_PER_RANK = 64 * 1024  # tokens of one step and rank the peer-visible id slot can hold
 
 
 @_lib.registrar
 def _register(lib) -> None:
     lib.hstd_fused_allreduce.argtypes = [C.POINTER(AllreduceArgs), C.c_void_p]
     lib.hstd_fused_allreduce.restype = C.c_int
+    lib.hstd_sparse_rows_mark.argtypes = [C.POINTER(AllreduceArgs), C.c_void_p]
+    lib.hstd_sparse_rows_mark.restype = C.c_int
+    for n in ("hstd_fused_allreduce_emulated", "hstd_sparse_rows_mark_emulated"):
+        getattr(lib, n).argtypes = [C.POINTER(AllreduceArgs), C.c_int, C.c_void_p]
+        getattr(lib, n).restype = C.c_int
     lib.hstd_allreduce_max_blocks.restype = C.c_int
     lib.hstd_allreduce_flag_words.argtypes = [C.c_int]
     lib.hstd_allreduce_flag_words.restype = C.c_int64
@@ -49,8 +61,7 @@ def _register(lib) -> None:
     lib.hstd_ipc_open.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
     lib.hstd_ipc_close.argtypes = [C.c_void_p]
     lib.hstd_ipc_free.argtypes = [C.c_void_p]
-    lib.hstd_enable_peer_access.argtypes = [C.c_int, C.c_int]
-    for n in ("hstd_ipc_alloc", "hstd_ipc_open", "hstd_ipc_close", "hstd_ipc_free", "hstd_enable_peer_access"):
+    for n in ("hstd_ipc_alloc", "hstd_ipc_open", "hstd_ipc_close", "hstd_ipc_free"):
         getattr(lib, n).restype = C.c_int
 
 
@@ -143,15 +154,25 @@ class P2PGroup:
         self.world, self.rank, self.device = comm.size(), comm.rank(), device
         self.total, self.buckets = total_elems, buckets
         self.max_blocks = lib.hstd_allreduce_max_blocks()
-        self.blocks = blocks or int(os.environ.get("HSTD_AR_BLOCKS", "48"))
+        # Blocks per bucket kernel.  Buckets that run underneath backward share the SMs with the GEMMs and are
+        # sized small; the trailing bucket(s) have no compute left to protect and take the whole budget.
+        self.blocks = blocks or int(os.environ.get("HSTD_AR_BLOCKS", "32"))
+        self.tail_blocks = int(os.environ.get("HSTD_AR_TAIL_BLOCKS", str(self.max_blocks)))
         w_bytes = _align(total_elems * 2, 256)
-        flag_words = lib.hstd_allreduce_flag_words(len(buckets) + 1)
+        # flag slots: one per bucket, one spare (collective tests / sweeps), one for the sparse-row marking
+        self.mark_slot = len(buckets) + 1
+        flag_words = lib.hstd_allreduce_flag_words(len(buckets) + 2)
         self.off_w, self.off_g, self.off_f = 0, w_bytes, 2 * w_bytes
-        self.arena = SymmetricArena(2 * w_bytes + flag_words * 4, device)
+        self.off_ids = _align(self.off_f + flag_words * 4, 256)
+        self.arena = SymmetricArena(self.off_ids + MAX_IDS_PER_RANK * 4, device)
         self.w16 = self.arena.view(self.off_w, total_elems, torch.bfloat16)
         self.g16 = self.arena.view(self.off_g, total_elems, torch.bfloat16)
-        self.epochs = torch.zeros((len(buckets) + 1) * self.max_blocks, dtype=torch.int32, device=device)
+        self.epochs = torch.zeros((len(buckets) + 2) * self.max_blocks, dtype=torch.int32, device=device)
+        self.sparse = next((b for b in buckets if getattr(b, "sparse", False)), None)
+        self.row_stamp = (torch.zeros(self.sparse.numel // self.sparse.row_elems, dtype=torch.int32, device=device)
+                          if self.sparse is not None else None)
         self.error = torch.zeros(1, dtype=torch.int32, device=device)
+        self._poll_host = None
         env_mode = os.environ.get("HSTD_AR_MODE")
         if force_mode is None and env_mode:
             force_mode = {"two_shot": AR_TWO_SHOT, "one_shot": AR_ONE_SHOT, "nvls": AR_NVLS}[env_mode]
@@ -159,6 +180,8 @@ class P2PGroup:
         for b in buckets:
             if force_mode is not None:
                 mode = force_mode
+            elif getattr(b, "sparse", False):  # sharded state is what the row filters work on
+                mode = AR_NVLS if self.arena.mc_ptr else AR_TWO_SHOT
             elif b.numel * 2 <= one_shot_bytes:
                 mode = AR_ONE_SHOT
             elif self.arena.mc_ptr:
@@ -166,6 +189,8 @@ class P2PGroup:
             else:
                 mode = AR_TWO_SHOT
             if mode == AR_NVLS and not self.arena.mc_ptr:
+                mode = AR_TWO_SHOT
+            if mode == AR_ONE_SHOT and getattr(b, "sparse", False):
                 mode = AR_TWO_SHOT
             self.modes.append(mode)
         # owned (fp32 master / moments) ranges, compact in bucket order
@@ -204,9 +229,24 @@ class P2PGroup:
         return full
 
     # ------------------------------------------------------------------ kernel launch
+    def ids_view(self, n: int) -> torch.Tensor:
+        """int32 [n] view of this rank's peer-visible token-id slot: the step's input_ids are copied straight
+        into it, so the sparse-row marking kernels of the other ranks can read them."""
+        if n > MAX_IDS_PER_RANK:
+            raise ValueError(f"batch of {n} tokens per rank exceeds the peer-visible id slot ({MAX_IDS_PER_RANK})")
+        return self.arena.view(self.off_ids, n, torch.int32)
+
     def make_args(self, bucket_index: int, start: int, numel: int, mode: int, update: bool, state=None, master=None,
-                  m=None, v=None, owned_offset: int = 0, blocks: Optional[int] = None) -> AllreduceArgs:
+                  m=None, v=None, owned_offset: int = 0, blocks: Optional[int] = None, rows: int = ROWS_ALL,
+                  world: Optional[int] = None, row_elem0: int = 0) -> AllreduceArgs:
         a = AllreduceArgs()
+        if rows != ROWS_ALL or bucket_index == self.mark_slot:
+            sp = self.sparse
+            a.row_stamp = self.row_stamp.data_ptr()
+            a.row_elems, a.rows, a.row_elem0 = sp.row_elems, rows, row_elem0
+            a.dense_rows, a.vocab_rows = sp.dense_rows, sp.vocab_rows
+            for r in range(self.world):
+                a.ids_peers[r] = self.arena.peer_ptrs[r] + self.off_ids
         for r in range(self.world):
             base = self.arena.peer_ptrs[r]
             a.w_peers[r] = base + self.off_w
@@ -217,61 +257,164 @@ class P2PGroup:
             a.g_mc = self.arena.mc_ptr + self.off_g
         a.epoch = self.epochs.data_ptr() + bucket_index * self.max_blocks * 4
         a.error = self.error.data_ptr()
+        if state is not None:
+            a.state = state.data_ptr()
         if update:
             a.master = master.data_ptr() + owned_offset * 4
             a.m = m.data_ptr() + owned_offset * 4
             a.v = v.data_ptr() + owned_offset * 4
-            a.state = state.data_ptr()
         a.start, a.numel = start, numel
         a.world, a.rank, a.bucket_index, a.mode = self.world, self.rank, bucket_index, mode
         a.update, a.blocks = int(update), blocks or self.blocks
+        if world == 1:
+            # this rank on its own (exposed-communication timing): "peer 0" is the local arena
+            a.world, a.rank = 1, 0
+            base = self.arena.peer_ptrs[self.rank]
+            a.w_peers[0], a.g_peers[0], a.flag_peers[0] = base + self.off_w, base + self.off_g, base + self.off_f
+            a.ids_peers[0] = base + self.off_ids
         return a
+
+    def launch_mark(self, args: AllreduceArgs, stream: Optional[torch.cuda.Stream] = None) -> None:
+        _lib.check(_lib.load().hstd_sparse_rows_mark(C.byref(args), _lib.stream_ptr(stream)), "sparse_rows_mark")
 
     def launch(self, args: AllreduceArgs, stream: Optional[torch.cuda.Stream] = None) -> None:
         _lib.check(_lib.load().hstd_fused_allreduce(C.byref(args), _lib.stream_ptr(stream)), "fused_allreduce")
 
+    def _raise(self, e: int) -> None:
+        raise RuntimeError(f"fused all-reduce watchdog: rank {self.rank} never heard from rank {e - 1} "
+                           "(peer died or diverged); aborting instead of hanging")
+
     def check_errors(self) -> None:
+        """Blocking read of the watchdog word (end of fit / epoch)."""
         e = int(self.error.item())
         if e:
-            raise RuntimeError(f"fused all-reduce watchdog: rank {self.rank} never heard from rank {e - 1} "
-                               "(peer died or diverged); aborting instead of hanging")
+            self._raise(e)
+
+    def poll_errors(self) -> None:
+        """Non-blocking health check for the training loop: looks at the copy of the watchdog word that
+        the PREVIOUS poll requested (pinned host memory, no stream synchronisation) and requests a new
+        one.  A dead peer therefore surfaces within two polling intervals instead of at the end of fit."""
+        if self._poll_host is None:
+            self._poll_host = torch.zeros(1, dtype=torch.int32).pin_memory()
+            self._poll_event = None
+        if self._poll_event is not None:
+            if not self._poll_event.query():
+                return  # previous copy still in flight (the device may be stuck in a watchdog spin)
+            e = int(self._poll_host.item())
+            if e:
+                self._raise(e)
+        self._poll_host.copy_(self.error, non_blocking=True)
+        self._poll_event = torch.cuda.Event()
+        self._poll_event.record()
 
     # ------------------------------------------------------------------ plan recording (called by DPEngine)
     def record_begin(self, plan) -> None:
-        self._plan_events = []
+        pass
 
-    def record_bucket(self, plan, bucket, state, master, m, v, overlap: bool = True) -> None:
+    def _fork_to_comm(self, plan, side_stream=None):
+        """Returns a callable that makes the comm stream wait for everything recorded so far on the main
+        stream and, when weight-gradient GEMMs run on the engine's side stream, on that stream too — the
+        main stream itself is never held up for a bucket."""
+        ev = torch.cuda.Event()
+        plan.keep.append(ev)
+        cs = self.comm_stream
+        ev2 = None
+        if side_stream is not None:
+            ev2 = torch.cuda.Event()
+            plan.keep.append(ev2)
+
+        def fork():
+            ev.record(torch.cuda.current_stream())
+            cs.wait_event(ev)
+            if ev2 is not None:
+                ev2.record(side_stream)
+                cs.wait_event(ev2)
+
+        return fork
+
+    def record_step_start(self, plan, state, master, m, v, n_ids: int) -> None:
+        """Row-sparse embedding bucket, start of the step (called right after the step prologue): mark the
+        rows that are live in this step, clear them in the local gradient arena, then give every idle row its
+        zero-gradient Adam step — all on the comm stream, underneath the forward pass."""
+        b = self.sparse
+        if b is None:
+            return
+        local = getattr(self, "debug_no_comm", False)
+        mode = self.modes[b.index]
+        start_o, n_o, off = self.owned[b.index]
+        mark = self.make_args(self.mark_slot, b.start, b.numel, mode, False, state, blocks=16,
+                              world=1 if local else None)
+        mark.n_ids = n_ids
+        if local:
+            idle = self.make_args(b.index, start_o, n_o, AR_TWO_SHOT, True, state, master, m, v, off, rows=ROWS_IDLE,
+                                  world=1, row_elem0=start_o - b.start)
+        else:
+            idle = self.make_args(b.index, b.start, b.numel, mode, True, state, master, m, v, off, rows=ROWS_IDLE)
+        fork = self._fork_to_comm(plan)
+        ev_marked = torch.cuda.Event()
+        plan.keep.append(ev_marked)
+        cs = self.comm_stream
+
+        def op():
+            fork()
+            self.launch_mark(mark, cs)
+            ev_marked.record(cs)
+            self.launch(idle, cs)
+
+        plan.launches += 2
+        plan.ops.append(op)
+        plan.names.append("sparse rows: mark + idle-row adamw@comm")
+        plan.uses_comm_stream = True
+        plan.rows_marked_event = ev_marked
+
+    def record_wait_rows_marked(self, plan) -> None:
+        """Main stream: the live gradient rows have been cleared (needed before the embedding scatter-add)."""
+        ev = getattr(plan, "rows_marked_event", None)
+        if ev is None:
+            return
+        plan.ops.append(lambda: torch.cuda.current_stream().wait_event(ev))
+        plan.names.append("wait(rows marked)")
+
+    def record_bucket(self, plan, bucket, state, master, m, v, overlap: bool = True, side_stream=None,
+                      last: bool = False) -> None:
         mode = self.modes[bucket.index]
         start_o, n_o, off = self.owned[bucket.index]
+        sparse = getattr(bucket, "sparse", False)
+        rows = ROWS_LIVE if sparse else ROWS_ALL
+        blocks = self.tail_blocks if (last or sparse) else self.blocks
         if getattr(self, "debug_no_comm", False):
             # timing aid for the "exposed communication" metric: the same optimizer work on the
             # owned slice, but no peer traffic and no cross-rank flags (ranks diverge: never train so)
-            args = self.make_args(bucket.index, start_o, n_o, AR_LOCAL, True, state, master, m, v, off)
+            if sparse:
+                args = self.make_args(bucket.index, start_o, n_o, AR_TWO_SHOT, True, state, master, m, v, off, blocks,
+                                      rows=ROWS_LIVE, world=1, row_elem0=start_o - bucket.start)
+            else:
+                args = self.make_args(bucket.index, start_o, n_o, AR_LOCAL, True, state, master, m, v, off, blocks)
         else:
-            args = self.make_args(bucket.index, bucket.start, bucket.numel, mode, True, state, master, m, v, off)
+            args = self.make_args(bucket.index, bucket.start, bucket.numel, mode, True, state, master, m, v, off, blocks,
+                                  rows=rows)
         plan.launches += 1
+        label = f"allreduce+adamw[{MODE_NAMES[mode]}{',live rows' if sparse else ''}]"
         if not overlap:
             plan.ops.append(lambda args=args: self.launch(args))
-            plan.names.append(f"allreduce+adamw[{MODE_NAMES[mode]}]")
+            plan.names.append(label)
             return
-        ev = torch.cuda.Event()
-        self._plan_events.append(ev)
+        fork = self._fork_to_comm(plan, side_stream)
         cs = self.comm_stream
 
-        def op(args=args, ev=ev):
-            ev.record(torch.cuda.current_stream())
-            cs.wait_event(ev)
+        def op(args=args, fork=fork):
+            fork()
             self.launch(args, cs)
 
         plan.ops.append(op)
-        plan.names.append(f"allreduce+adamw[{MODE_NAMES[mode]}]@comm")
+        plan.names.append(label + "@comm")
         plan.uses_comm_stream = True
 
     def record_end(self, plan) -> None:
         if not getattr(plan, "uses_comm_stream", False):
             return
         ev = torch.cuda.Event()
-        self._plan_events.append(ev)
+        plan.keep.append(ev)
         cs = self.comm_stream
 
         def op(ev=ev):
@@ -280,9 +423,72 @@ class P2PGroup:
 
         plan.ops.append(op)
         plan.names.append("join(comm)")
-        plan.keep_events = self._plan_events
 
     def describe(self) -> Dict:
         return {"arena": self.arena.kind, "nvls": bool(self.arena.mc_ptr), "blocks": self.blocks,
-                "buckets": [{"mb": round(b.numel * 2 / 2 ** 20, 2), "mode": MODE_NAMES[m]}
+                "tail_blocks": self.tail_blocks,
+                "buckets": [{"mb": round(b.numel * 2 / 2 ** 20, 2), "mode": MODE_NAMES[m],
+                             **({"row_sparse": True} if getattr(b, "sparse", False) else {})}
                             for b, m in zip(self.buckets, self.modes)]}
+
+
+class EmulatedP2P:
+    """``world`` ranks' arenas on ONE GPU, driven through the emulated entry points: a single cooperative
+    grid runs every rank's blocks with the same per-block code as the real kernels (flag barriers, peer
+    loads / stores, fused AdamW, row filters).  For tests and profiling on a box with fewer GPUs than ranks;
+    separate launches that wait on one another are not an option on one device (nothing guarantees they are
+    co-scheduled), hence the one-kernel form.  Two-shot and one-shot only (NVLS needs a multicast mapping)."""
+
+    def __init__(self, world: int, total_elems: int, num_buckets: int, device: torch.device, row_elems: int = 0,
+                 rows: int = 0, blocks: int = 8):
+        lib = _lib.load()
+        self.world, self.total, self.device, self.blocks = world, total_elems, device, blocks
+        self.max_blocks = lib.hstd_allreduce_max_blocks()
+        nflag = lib.hstd_allreduce_flag_words(num_buckets + 2)
+        self.mark_slot = num_buckets + 1
+        z = lambda n, dt: [torch.zeros(n, dtype=dt, device=device) for _ in range(world)]  # noqa: E731
+        self.w16, self.g16 = z(total_elems, torch.bfloat16), z(total_elems, torch.bfloat16)
+        self.flags = z(nflag, torch.int32)
+        self.epochs = z((num_buckets + 2) * self.max_blocks, torch.int32)
+        self.errors = z(1, torch.int32)
+        self.ids = z(MAX_IDS_PER_RANK, torch.int32)
+        self.row_elems = row_elems
+        self.stamps = z(max(rows, 1), torch.int32)
+
+    def args(self, rank: int, bucket_index: int, start: int, numel: int, mode: int, update: bool, state=None,
+             master=None, m=None, v=None, rows: int = ROWS_ALL, n_ids: int = 0, dense_rows: int = 0,
+             vocab_rows: int = 0) -> AllreduceArgs:
+        a = AllreduceArgs()
+        for r in range(self.world):
+            a.w_peers[r], a.g_peers[r] = self.w16[r].data_ptr(), self.g16[r].data_ptr()
+            a.flag_peers[r], a.ids_peers[r] = self.flags[r].data_ptr(), self.ids[r].data_ptr()
+        a.epoch = self.epochs[rank].data_ptr() + bucket_index * self.max_blocks * 4
+        a.error = self.errors[rank].data_ptr()
+        if state is not None:
+            a.state = state.data_ptr()
+        if update:
+            a.master, a.m, a.v = master.data_ptr(), m.data_ptr(), v.data_ptr()
+        a.start, a.numel, a.world, a.rank = start, numel, self.world, rank
+        a.bucket_index, a.mode, a.update, a.blocks = bucket_index, mode, int(update), self.blocks
+        # rank 0's stamps serve every emulated rank in the all-reduce (the marking leaves them identical)
+        a.row_stamp = self.stamps[rank if bucket_index == self.mark_slot else 0].data_ptr()
+        a.row_elems, a.rows, a.n_ids, a.dense_rows, a.vocab_rows = self.row_elems, rows, n_ids, dense_rows, vocab_rows
+        return a
+
+    def _array(self, per_rank):
+        arr = (AllreduceArgs * self.world)()
+        for r, a in enumerate(per_rank):
+            arr[r] = a
+        return arr
+
+    def allreduce(self, per_rank) -> None:
+        _lib.check(_lib.load().hstd_fused_allreduce_emulated(self._array(per_rank), self.world, _lib.stream_ptr(None)),
+                   "fused_allreduce_emulated")
+
+    def mark(self, per_rank) -> None:
+        _lib.check(_lib.load().hstd_sparse_rows_mark_emulated(self._array(per_rank), self.world, _lib.stream_ptr(None)),
+                   "sparse_rows_mark_emulated")
+
+    def check_errors(self) -> None:
+        for r, e in enumerate(self.errors):
+            assert int(e.item()) == 0, f"emulated rank {r}: watchdog fired ({int(e.item())})"

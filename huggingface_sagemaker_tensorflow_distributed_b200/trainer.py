@@ -135,6 +135,7 @@ class SequenceClassifier:
         device = self.backend.device
         t_fit = time.time()
         samples_seen = 0
+        health_every = max(1, min(log_every, 50)) if log_every > 0 else 50
         for epoch in range(epochs):
             meter = _Meter(device, self.backend)
             t0 = time.time()
@@ -143,6 +144,8 @@ class SequenceClassifier:
                     break
                 with nvtx_range("train_step"):
                     meter.update(self.backend.train_step(feats, labels))
+                if (step + 1) % health_every == 0 and hasattr(self.backend, "poll_health"):
+                    self.backend.poll_health()  # a dead peer aborts the job now, not at the end of fit
                 if verbose and log_every > 0 and (step + 1) % log_every == 0:
                     r = meter.read()
                     dt = time.time() - t0
@@ -152,6 +155,8 @@ class SequenceClassifier:
                     print(msg, flush=True)
                     self._sink({"event": "train_progress", "epoch": epoch + 1, "step": step + 1, **r})
             r = meter.read()
+            if hasattr(self.backend, "finish"):
+                self.backend.finish()  # epoch boundary: blocking read of the watchdog word
             samples_seen += int(r.pop("count"))
             logs = dict(r)
             for cb in callbacks:

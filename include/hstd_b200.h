@@ -150,7 +150,8 @@ int hstd_ln_bwd(const hstd_ln_bwd_args* args, void* stream);
 int64_t hstd_ln_bwd_partials_floats(int d);
 
 /* Column sums of a bf16 [M,N] matrix into bf16 [N] (bias gradients).  `partials`: scratch
- * of hstd_colsum_partials_floats(N) floats. */
+ * of hstd_colsum_partials_floats(N) floats.  `x` must be 16-byte aligned and `ld` (elements)
+ * a multiple of 8: rows are read with 16-byte vector loads; anything else is refused. */
 int hstd_colsum(const void* x, int64_t ld, int M, int N, void* out_bf16, float* partials, void* stream);
 int64_t hstd_colsum_partials_floats(int N);
 
@@ -163,8 +164,12 @@ int64_t hstd_colsum_partials_floats(int N);
  *   - N is limited to hstd_colsum_noalloc_max_n() (4096); larger N is refused with an error
  *     and should go through hstd_colsum;
  *   - the call makes no cudaMalloc/cudaFree and uses no allocating library routine;
+ *   - `x` must be 16-byte aligned and `ld` a multiple of 8 elements, as for hstd_colsum
+ *     (refused with an error otherwise, never a fault);
  *   - the first call on each device looks up the array's device address (with that device
- *     current); make that first call before starting any stream capture;
+ *     current); make that first call before starting any stream capture.  The address is
+ *     cached for the life of the process: it does not survive a cudaDeviceReset(), after
+ *     which this entry point must not be used again in that process;
  *   - all calls on a device share the one array: two calls whose kernels can run at the same
  *     time (different streams, no dependency between them) race on it — order them.  The
  *     array keeps the previous call's partial sums; nothing needs clearing, every cell that is
@@ -260,8 +265,42 @@ typedef struct hstd_allreduce_args {
   const hstd_step_state* state;
   int64_t start, numel; /* elements; numel % (8*world) == 0 */
   int32_t world, rank, bucket_index, mode, update, blocks;
+  /* row-sparse buckets (see below); all zero for an ordinary bucket */
+  void* row_stamp;     /* uint32 per bucket row: == state->step when the row is live in this step */
+  void* ids_peers[8];  /* hstd_sparse_rows_mark: this step's int32 token ids of every rank */
+  int32_t row_elems;   /* elements per row (the hidden size) */
+  int32_t rows;        /* HSTD_AR_ROWS_* filter of this launch */
+  int32_t n_ids;       /* ids per rank */
+  int32_t dense_rows;  /* leading rows of the bucket that are live in every step */
+  int32_t vocab_rows;  /* rows addressable by an id, following the dense ones */
+  int32_t reserved_;
+  int64_t row_elem0;   /* bucket-relative element offset of `start` when a launch covers part of a row-sparse bucket */
 } hstd_allreduce_args;
 int hstd_fused_allreduce(const hstd_allreduce_args* args, void* stream);
+
+/* Row-sparse form for the embedding bucket (Horovod ships IndexedSlices gradients by allgather unless
+ * sparse_as_dense is set, which the reference does not do — scripts/train.py:114; Keras' Adam then
+ * still decays m / v and steps EVERY row).  The bucket is a stack of rows of `row_elems` elements:
+ * `dense_rows` always-live rows (LayerNorm, position, token-type tables) followed by `vocab_rows`
+ * word-embedding rows.  Per step:
+ *   1. hstd_sparse_rows_mark, as soon as the batch is on the device: flag barrier, every rank reads
+ *      every rank's ids (peer loads), stamps the rows somebody will produce a gradient for with the
+ *      step number and clears exactly those rows of its own gradient arena.
+ *   2. hstd_fused_allreduce(rows = HSTD_AR_ROWS_IDLE), any time after 1: rows nobody touches have a
+ *      zero gradient everywhere, so the owner applies the Adam step (m, v decay; w moves by its
+ *      history) and broadcasts the new bf16 row with no reduction and no barrier — off the critical
+ *      path, under the forward pass (no rank reads an idle row during the step).
+ *   3. hstd_fused_allreduce(rows = HSTD_AR_ROWS_LIVE) after backward: reduce + AdamW + broadcast of
+ *      the live rows only.  Together 2 and 3 equal the dense update exactly. */
+enum { HSTD_AR_ROWS_ALL = 0, HSTD_AR_ROWS_LIVE = 1, HSTD_AR_ROWS_IDLE = 2 };
+int hstd_sparse_rows_mark(const hstd_allreduce_args* args, void* stream);
+
+/* Single-GPU emulation of a `world`-rank launch for tests and profiling on a box with fewer GPUs
+ * than ranks: one cooperative grid runs every rank's blocks (the same per-block code as the real
+ * kernels, flag barriers included) over `world` arenas that all live on the current device.
+ * `per_rank[r]` is what rank r would pass to the real entry point (two-shot / one-shot only). */
+int hstd_fused_allreduce_emulated(const hstd_allreduce_args* per_rank, int world, void* stream);
+int hstd_sparse_rows_mark_emulated(const hstd_allreduce_args* per_rank, int world, void* stream);
 int hstd_allreduce_max_blocks(void);
 int64_t hstd_allreduce_flag_words(int num_buckets);
 
@@ -272,7 +311,6 @@ int hstd_ipc_alloc(int64_t bytes, void** ptr, void* handle64);
 int hstd_ipc_open(const void* handle64, void** ptr);
 int hstd_ipc_close(void* ptr);
 int hstd_ipc_free(void* ptr);
-int hstd_enable_peer_access(int dev, int peer);
 
 /* ------------------------------------------------------------------ host runtime: tokenizer (N6)
  * Native WordPiece tokenizer: the C++ side of AutoTokenizer.from_pretrained(...)(text,

@@ -95,6 +95,131 @@ def check_collectives():
         log("OK fused_update", p2p.MODE_NAMES[mode])
 
 
+def check_row_sparse():
+    """mark -> idle rows -> live rows on real peers == dense reduce + AdamW (gathered fp32 reference)."""
+    W, R, dev = hvd.size(), hvd.rank(), comm.device()
+    d, dense_rows, vocab, n_ids = 256, 6, 2000, 160
+    rows = dense_rows + vocab
+    while (rows * d) % (8 * W):
+        rows += 1
+    vocab = rows - dense_rows
+    total = rows * d
+    b = Bucket(0, 0, total, [], sparse=True, row_elems=d, dense_rows=dense_rows, vocab_rows=vocab)
+    grp = p2p.P2PGroup(total, [b], dev)
+    mode = grp.modes[0]
+    torch.manual_seed(3)
+    w0 = torch.randn(total, device=dev)
+    n = total // W
+    master, m, v = w0[R * n:(R + 1) * n].clone(), torch.zeros(n, device=dev), torch.zeros(n, device=dev)
+    grp.w16.copy_(w0.bfloat16())
+    grp.g16.fill_(float("nan"))
+    rm, rmm, rv = w0.clone(), torch.zeros(total, device=dev), torch.zeros(total, device=dev)
+    rw = torch.empty(total, dtype=torch.bfloat16, device=dev)
+    st = K.new_step_state(dev, seed=1)
+    ids_slot = grp.ids_view(n_ids)
+    for step in range(4):
+        K.step_prologue(st, 1e-2, "constant", 0, 0, 0.9, 0.999, 1e-7, 0.0)
+        g = torch.Generator(device="cpu").manual_seed(50 + step)
+        ids = [torch.randint(0, vocab, (n_ids,), generator=g, dtype=torch.int32) for _ in range(W)]
+        ids_slot.copy_(ids[R])
+        mark = grp.make_args(grp.mark_slot, 0, total, mode, False, st, blocks=8)
+        mark.n_ids = n_ids
+        grp.launch_mark(mark)
+        grp.launch(grp.make_args(0, 0, total, mode, True, st, master, m, v, 0, rows=p2p.ROWS_IDLE))
+        gr = grp.g16.view(rows, d)
+        torch.manual_seed(900 + 10 * step + R)
+        gr[:dense_rows] = (torch.randn(dense_rows, d, device=dev) * 0.1).bfloat16()
+        upd = (torch.randn(n_ids, d, device=dev) * 0.1).bfloat16()
+        for k, i in enumerate(ids[R].tolist()):
+            gr[dense_rows + i] += upd[k]
+        live = torch.unique(torch.cat(ids).long().to(dev)) + dense_rows
+        assert torch.isfinite(gr[live].float()).all(), "a live row was not cleared by the marking kernel"
+        mine = torch.zeros(rows, d, device=dev)
+        mine[:dense_rows] = gr[:dense_rows].float()
+        mine[live] = gr[live].float()
+        torch.cuda.synchronize()
+        dist.barrier()
+        avg = torch.stack(gather_all(mine)).sum(0).view(-1) / W
+        grp.launch(grp.make_args(0, 0, total, mode, True, st, master, m, v, 0, rows=p2p.ROWS_LIVE, blocks=grp.tail_blocks))
+        torch.cuda.synchronize()
+        dist.barrier()
+        if mode == p2p.AR_NVLS:  # the switch hands back a bf16-rounded sum
+            K.adamw_flat(st, avg.bfloat16(), rm, rmm, rv, rw)
+        else:
+            _ref_adam(st, avg, rm, rmm, rv, rw)
+        torch.cuda.synchronize()
+    grp.check_errors()
+    tol = 2e-3 if mode == p2p.AR_NVLS else 1e-5
+    full = grp.gather_owned(master)
+    assert torch.allclose(full, rm, atol=tol, rtol=tol), (full - rm).abs().max().item()
+    same = gather_all(grp.w16)
+    assert all(torch.equal(same[0], s) for s in same), "weights differ across ranks"
+    assert (grp.w16.float() - rm).abs().max().item() <= 0.02 * rm.abs().max().item()
+    log("OK row_sparse", p2p.MODE_NAMES[mode])
+
+
+def _tiny_fit(samples, epochs=1, seed=5, on_step=None):
+    from huggingface_sagemaker_tensorflow_distributed_b200 import trainer as T
+    from huggingface_sagemaker_tensorflow_distributed_b200.data import BatchedDataset, synthetic_imdb
+    from huggingface_sagemaker_tensorflow_distributed_b200.optim import Adam
+    W, R, dev = hvd.size(), hvd.rank(), comm.device()
+    model = T.AutoModelForSequenceClassification.from_pretrained("tiny-distilbert-gpu", device=dev, seed=seed, bucket_mb=0.5)
+    ds = synthetic_imdb(model.cfg, samples, 128, seed=2)
+    opt = hvd.DistributedOptimizer(Adam(learning_rate=1e-4 * W))
+    model.compile(optimizer=opt, loss=T.SparseCategoricalCrossentropy(from_logits=True))
+    bds = BatchedDataset(ds, 4, R, W)
+    hist = model.fit(bds, epochs=epochs, verbose=0, log_every=2,
+                     callbacks=[hvd.callbacks.BroadcastGlobalVariablesCallback(0)] + ([on_step] if on_step else []))
+    return model, hist, len(bds)
+
+
+def check_uneven():
+    """65 samples: the strided shards differ by one sample; both ranks must run the same number of steps."""
+    model, hist, steps = _tiny_fit(65)
+    n = torch.tensor([steps], device=comm.device())
+    parts = gather_all(n)
+    assert all(int(p.item()) == steps for p in parts), [int(p.item()) for p in parts]
+    loss = hist.history["loss"][0]
+    assert loss == loss
+    log("OK uneven shards", steps, "steps on every rank")
+
+
+def check_dead_peer():
+    """Rank 1 dies without warning after a few steps; rank 0 must fail with the watchdog error."""
+    import signal
+    import time
+    from huggingface_sagemaker_tensorflow_distributed_b200 import trainer as T
+    from huggingface_sagemaker_tensorflow_distributed_b200.data import BatchedDataset, synthetic_imdb
+    from huggingface_sagemaker_tensorflow_distributed_b200.optim import Adam
+    W, R, dev = hvd.size(), hvd.rank(), comm.device()
+    model = T.AutoModelForSequenceClassification.from_pretrained("tiny-distilbert-gpu", device=dev, seed=5, bucket_mb=0.5)
+    ds = synthetic_imdb(model.cfg, 4 * 4000 * W, 128, seed=2)
+    opt = hvd.DistributedOptimizer(Adam(learning_rate=1e-4 * W))
+    model.compile(optimizer=opt, loss=T.SparseCategoricalCrossentropy(from_logits=True))
+    model.backend.setup_training(opt, 10 ** 6, 4, 128)
+    model.broadcast_state(0)
+    batches = list(BatchedDataset(ds, 4, R, W, max_batches=8))
+    for i in range(8):
+        model.backend.train_step(*batches[i])
+    torch.cuda.synchronize()
+    if R == 1:
+        os.kill(os.getpid(), signal.SIGKILL)
+    t0 = time.time()
+    try:
+        for i in range(100000):
+            model.backend.train_step(*batches[i % 8])
+            if (i + 1) % 20 == 0:
+                model.backend.poll_health()
+            if time.time() - t0 > 60:
+                break
+        model.backend.finish()
+    except RuntimeError as e:
+        print(f"rank {R}: {e}", flush=True)
+        os._exit(3)
+    print("rank 0 never noticed the dead peer", flush=True)
+    os._exit(0)
+
+
 def _ref_adam(st, g_fp32, w, m, v, wb):
     s = K.read_step_state(st)
     m.mul_(s.beta1).add_(g_fp32, alpha=1 - s.beta1)
@@ -138,6 +263,11 @@ if __name__ == "__main__":
     which = sys.argv[1] if len(sys.argv) > 1 else "all"
     if which in ("all", "collectives"):
         check_collectives()
+        check_row_sparse()
+    if which == "uneven":
+        check_uneven()
+    if which == "dead_peer":
+        check_dead_peer()
     if which in ("all", "training"):
         check_training()
     dist.barrier()

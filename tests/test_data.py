@@ -42,3 +42,22 @@ def test_channel_npz_roundtrip(tmp_path):
     assert got.input_ids.shape == (10, 32) and (got.input_ids[:, 16:] == cfg.pad_token_id).all()
     train, test = build_datasets(cfg, train_samples=5, test_samples=6, seq_len=32, seed=0, train_channel=str(tmp_path))
     assert len(train) == 10 and len(test) == 6
+
+
+def test_uneven_shards_take_the_same_number_of_steps():
+    """65 samples over 8 ranks at batch 8: rank 0 holds 9 samples, the others 8.  Every rank must still
+    iterate the same number of batches (the gradient all-reduce is a collective); the short ranks pad
+    with ignored rows.  Both the Python iterator and the native prefetching loader."""
+    cfg = resolve_config("tiny-bert")
+    ds = synthetic_imdb(cfg, 65, 16)
+    for prefetch in (False, True):
+        lens, seen = [], 0
+        for r in range(8):
+            b = BatchedDataset(ds, 8, r, 8, prefetch=prefetch)
+            batches = [(f["input_ids"].clone(), l.clone()) for f, l in b]
+            assert len(batches) == len(b)
+            lens.append(len(batches))
+            seen += sum(int((l != IGNORE_LABEL).sum()) for _, l in batches)
+            if r > 0:  # the extra batch of a short rank is all padding
+                assert (batches[-1][1] == IGNORE_LABEL).all()
+        assert lens == [2] * 8 and seen == 65

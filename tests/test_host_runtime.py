@@ -191,6 +191,36 @@ def test_bucket_plan_matches_python_statement_and_model_layout():
         host.bucket_plan([0, 4], [8, 12], 16)  # overlapping parameters
 
 
+def test_embedding_block_is_one_row_sparse_bucket():
+    """Real model layouts: encoder + head parameters are bucketed greedily, the embedding block (complete only
+    when backward ends) is a single bucket that is a stack of hidden-size rows."""
+    from huggingface_sagemaker_tensorflow_distributed_b200.models.configuration import resolve_config
+    from huggingface_sagemaker_tensorflow_distributed_b200.models.engine import ALIGN, backward_ready_order, param_shapes
+    from huggingface_sagemaker_tensorflow_distributed_b200.parallel.dp_engine import plan_buckets_with_embeddings
+    import math
+
+    for name in ("distilbert-base-uncased", "bert-base-uncased", "roberta-large"):
+        cfg = resolve_config(name)
+        shapes, slots, cur = param_shapes(cfg), {}, 0
+        order = backward_ready_order(cfg)
+        for n in order:
+            numel = math.prod(shapes[n])
+            slots[n] = SimpleNamespace(offset=cur, numel=numel, shape=shapes[n], end=cur + (numel + ALIGN - 1) // ALIGN * ALIGN)
+            cur = slots[n].end
+        for world in (2, 4, 8):
+            bs = plan_buckets_with_embeddings(slots, order, 16 * (1 << 20) // 2, world, row_sparse=True)
+            assert [n for b in bs for n in b.names] == order
+            assert all(a.end == b.start for a, b in zip(bs, bs[1:])) and bs[-1].end == cur
+            e = bs[-1]
+            assert e.sparse and e.row_elems == cfg.hidden_size and e.vocab_rows == cfg.vocab_size
+            assert e.names[-1] == "emb.word.weight" and all(n.startswith("emb.") for n in e.names)
+            assert e.start + e.dense_rows * e.row_elems == slots["emb.word.weight"].offset
+            assert e.numel % (8 * world) == 0 and not any(b.sparse for b in bs[:-1])
+            assert len(bs) >= 6  # fine enough to overlap: 16 MiB buckets
+        dense = plan_buckets_with_embeddings(slots, order, 16 * (1 << 20) // 2, 1, row_sparse=False)
+        assert not dense[-1].sparse and dense[-1].names == bs[-1].names
+
+
 def test_bucket_tracker_releases_in_order_and_honours_exemptions():
     from huggingface_sagemaker_tensorflow_distributed_b200.ops import host
 

@@ -75,3 +75,19 @@ def test_rejects_widths_beyond_the_builtin_scratch():
     x = torch.ones(64, max_n, dtype=torch.bfloat16, device="cuda")
     got, want = _both(lib, x)
     assert (got.float() == 64).all() and (want.float() == 64).all()
+
+
+def test_refuses_misaligned_input_instead_of_faulting():
+    """Rows are read eight bf16 at a time; a caller working with raw pointers gets an error code for
+    an odd base address or row stride, not a misaligned-address fault that would poison the context."""
+    lib = _lib()
+    x = torch.ones(16, 72, dtype=torch.bfloat16, device="cuda")
+    out = torch.zeros(64, dtype=torch.bfloat16, device="cuda")
+    s = torch.cuda.current_stream().cuda_stream
+    assert lib.hstd_colsum_noalloc(x.data_ptr() + 2, 72, 16, 64, out.data_ptr(), s) != 0
+    assert b"16-byte aligned" in lib.hstd_last_error()
+    assert lib.hstd_colsum_noalloc(x.data_ptr(), 68, 16, 64, out.data_ptr(), s) != 0
+    assert b"multiple of 8" in lib.hstd_last_error()
+    assert lib.hstd_colsum_noalloc(x.data_ptr(), 72, 16, 64, out.data_ptr(), s) == 0
+    torch.cuda.synchronize()
+    assert (out.float() == 16).all()
