@@ -92,19 +92,6 @@ __device__ __forceinline__ void tma_load_4d(void* smem_dst, const CUtensorMap* m
       : "memory");
 }
 
-// Same, multicast to every CTA of the cluster named in `cta_mask`: the tile lands at the same
-// smem offset in each destination CTA and completes `bytes` on the mbarrier at the same offset.
-__device__ __forceinline__ void tma_load_4d_multicast(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1,
-                                                      int c2, int c3, uint16_t cta_mask) {
-  asm volatile(
-      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
-      " [%0], [%1, {%4, %5, %6, %7}], [%2], %3;"
-      :
-      : "r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "h"(cta_mask), "r"(c0),
-        "r"(c1), "r"(c2), "r"(c3)
-      : "memory");
-}
-
 // 2-SM (cta_group::2) form: both CTAs of a pair issue it; `bar_cluster_addr` is the
 // shared::cluster address of the LEADER's mbarrier (see mapa_shared), so the bytes landing in
 // either CTA complete on the leader's barrier.
