@@ -30,7 +30,12 @@ namespace hstd {
 
 constexpr int AR_MAX_WORLD = 8;
 constexpr int AR_MAX_BLOCKS = 128;
-constexpr int AR_THREADS = 512;
+// Small blocks with a small register footprint: a tcgen05 GEMM CTA holds ~54 K of the SM's 64 K registers and
+// ~200 KB of its shared memory, an attention CTA ~48 K registers.  A 128-thread block at <= 85 registers (and
+// no shared memory) fits NEXT to them, so bucket kernels running underneath backward share SMs with the
+// compute kernels instead of displacing their (persistent, statically scheduled) CTAs.
+constexpr int AR_THREADS = 128;
+constexpr int AR_MIN_BLOCKS_PER_SM = 6;
 constexpr long long AR_TIMEOUT_CYCLES = 20ll * 1000 * 1000 * 1000;  // ~10 s at 2 GHz
 
 struct ArKernelParams {
@@ -132,20 +137,81 @@ __device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
                     pack_bf16x2_dev(f[6], f[7]));
 }
 
-// AdamW on 8 consecutive owned elements at compact index `o`; returns the new bf16 weights.
-__device__ __forceinline__ uint4 adam8(const AdamScalars& sc, const ArKernelParams& p, int64_t o, const float (&g)[8]) {
-  float4 w0 = *reinterpret_cast<float4*>(p.master + o), w1 = *reinterpret_cast<float4*>(p.master + o + 4);
-  float4 m0 = *reinterpret_cast<float4*>(p.m + o), m1 = *reinterpret_cast<float4*>(p.m + o + 4);
-  float4 v0 = *reinterpret_cast<float4*>(p.v + o), v1 = *reinterpret_cast<float4*>(p.v + o + 4);
-  adam_update(sc, g[0], w0.x, m0.x, v0.x); adam_update(sc, g[1], w0.y, m0.y, v0.y);
-  adam_update(sc, g[2], w0.z, m0.z, v0.z); adam_update(sc, g[3], w0.w, m0.w, v0.w);
-  adam_update(sc, g[4], w1.x, m1.x, v1.x); adam_update(sc, g[5], w1.y, m1.y, v1.y);
-  adam_update(sc, g[6], w1.z, m1.z, v1.z); adam_update(sc, g[7], w1.w, m1.w, v1.w);
-  *reinterpret_cast<float4*>(p.master + o) = w0; *reinterpret_cast<float4*>(p.master + o + 4) = w1;
-  *reinterpret_cast<float4*>(p.m + o) = m0; *reinterpret_cast<float4*>(p.m + o + 4) = m1;
-  *reinterpret_cast<float4*>(p.v + o) = v0; *reinterpret_cast<float4*>(p.v + o + 4) = v1;
-  const float w[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+// fp32 master weight + Adam moments of 8 consecutive owned elements (compact index `o`), loaded ahead of
+// use so that several vectors' worth of HBM requests are in flight per thread.
+struct AdamState8 {
+  float4 w0, w1, m0, m1, v0, v1;
+};
+__device__ __forceinline__ AdamState8 adam_load8(const ArKernelParams& p, int64_t o) {
+  AdamState8 s;
+  s.w0 = *reinterpret_cast<const float4*>(p.master + o); s.w1 = *reinterpret_cast<const float4*>(p.master + o + 4);
+  s.m0 = *reinterpret_cast<const float4*>(p.m + o); s.m1 = *reinterpret_cast<const float4*>(p.m + o + 4);
+  s.v0 = *reinterpret_cast<const float4*>(p.v + o); s.v1 = *reinterpret_cast<const float4*>(p.v + o + 4);
+  return s;
+}
+// AdamW on those 8 elements; stores the new state and returns the new bf16 weights.
+__device__ __forceinline__ uint4 adam8(const AdamScalars& sc, const ArKernelParams& p, int64_t o, AdamState8& s,
+                                       const float (&g)[8]) {
+  adam_update(sc, g[0], s.w0.x, s.m0.x, s.v0.x); adam_update(sc, g[1], s.w0.y, s.m0.y, s.v0.y);
+  adam_update(sc, g[2], s.w0.z, s.m0.z, s.v0.z); adam_update(sc, g[3], s.w0.w, s.m0.w, s.v0.w);
+  adam_update(sc, g[4], s.w1.x, s.m1.x, s.v1.x); adam_update(sc, g[5], s.w1.y, s.m1.y, s.v1.y);
+  adam_update(sc, g[6], s.w1.z, s.m1.z, s.v1.z); adam_update(sc, g[7], s.w1.w, s.m1.w, s.v1.w);
+  *reinterpret_cast<float4*>(p.master + o) = s.w0; *reinterpret_cast<float4*>(p.master + o + 4) = s.w1;
+  *reinterpret_cast<float4*>(p.m + o) = s.m0; *reinterpret_cast<float4*>(p.m + o + 4) = s.m1;
+  *reinterpret_cast<float4*>(p.v + o) = s.v0; *reinterpret_cast<float4*>(p.v + o + 4) = s.v1;
+  const float w[8] = {s.w0.x, s.w0.y, s.w0.z, s.w0.w, s.w1.x, s.w1.y, s.w1.z, s.w1.w};
   return pack8(w);
+}
+
+// Vectors per thread whose peer loads are issued before the first one is consumed.  A peer / multimem load
+// is a ~2-3 us round trip through the switch: with ONE 16-byte request per thread a bucket kernel moved
+// < 100 GB/s, the comm stream fell behind backward and the backlog showed up as exposed communication.
+// 32 landing registers per thread: 8 multimem loads (NVLS) or 8 / WORLD vectors x WORLD peers (two-shot).
+template <int WORLD, int MODE>
+__host__ __device__ constexpr int ar_unroll() {
+  return MODE == 2 ? 8 : (MODE == 1 ? 1 : (WORLD <= 2 ? 4 : (WORLD <= 4 ? 2 : 1)));
+}
+constexpr int AR_UPDATE_UNROLL = 2;  // vectors whose optimizer state (24 floats each) is fetched together
+
+template <int WORLD, int MODE>
+__device__ __forceinline__ void load_vec(const ArKernelParams& p, int64_t elem, uint4 (&raw)[MODE == 2 ? 1 : WORLD]) {
+  if (MODE == 2) {
+    raw[0] = multimem_ld_reduce_bf16x8(p.g_mc + elem);
+  } else {
+#pragma unroll
+    for (int r = 0; r < WORLD; ++r) raw[r] = ld_peer_16B(p.g_peers[r] + elem);
+  }
+}
+// Sum over ranks (fixed rank order: every rank would form the same sum) x 1/world.
+template <int WORLD, int MODE>
+__device__ __forceinline__ void reduce_vec(const ArKernelParams& p, const uint4 (&raw)[MODE == 2 ? 1 : WORLD], float (&g)[8]) {
+  if (MODE == 2) {
+    unpack8(raw[0], g);
+  } else {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) g[j] = 0.f;
+#pragma unroll
+    for (int r = 0; r < WORLD; ++r) {
+      float t[8];
+      unpack8(raw[r], t);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) g[j] += t[j];
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) g[j] *= p.inv_world;
+}
+template <int WORLD, int MODE>
+__device__ __forceinline__ void store_all_ranks(const ArKernelParams& p, __nv_bfloat16* const* peers, __nv_bfloat16* mc,
+                                                int64_t elem, const uint4& v) {
+  if (MODE == 1) {
+    *reinterpret_cast<uint4*>(peers[p.rank] + elem) = v;
+  } else if (MODE == 2) {
+    multimem_st_16B(mc + elem, v);
+  } else {
+#pragma unroll
+    for (int r = 0; r < WORLD; ++r) st_peer_16B(peers[(p.rank + r) % WORLD] + elem, v);
+  }
 }
 
 // Row filter of a launch over a row-sparse bucket.
@@ -181,57 +247,96 @@ __device__ __forceinline__ void allreduce_block(const ArKernelParams& p, int blo
   const int64_t stride = int64_t(nblocks) * blockDim.x;
   const uint32_t row_vecs = ROWS != ROWS_ALL ? uint32_t(p.row_elems) / 8u : 1u;
 
-  for (int64_t i = block * int64_t(blockDim.x) + threadIdx.x; i < nvec; i += stride) {
-    if (ROWS != ROWS_ALL) {
-      const bool live = p.row_stamp[uint32_t(p.row_vec0 + first + i) / row_vecs] == stamp;
-      if (live != (ROWS == ROWS_LIVE)) continue;
-    }
-    const int64_t elem = p.start + (first + i) * 8;  // arena element offset
-    float g[8];
-    if (ROWS == ROWS_IDLE) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) g[j] = 0.f;
-    } else if (MODE == 2) {
-      unpack8(multimem_ld_reduce_bf16x8(p.g_mc + elem), g);
-    } else {
-      uint4 raw[WORLD];
-#pragma unroll
-      for (int r = 0; r < WORLD; ++r) raw[r] = ld_peer_16B(p.g_peers[r] + elem);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) g[j] = 0.f;
-#pragma unroll
-      for (int r = 0; r < WORLD; ++r) {  // fixed rank order: every rank would form the same sum
-        float t[8];
-        unpack8(raw[r], t);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) g[j] += t[j];
-      }
-    }
-#pragma unroll
-    for (int j = 0; j < 8; ++j) g[j] *= p.inv_world;
+  constexpr int NL = MODE == 2 ? 1 : WORLD;  // 16-byte loads per vector
+  const int64_t t0 = block * int64_t(blockDim.x) + threadIdx.x;
+  auto selected = [&](int64_t i) -> bool {
+    if (i >= nvec) return false;
+    if (ROWS == ROWS_ALL) return true;
+    const bool live = p.row_stamp[uint32_t(p.row_vec0 + first + i) / row_vecs] == stamp;
+    return live == (ROWS == ROWS_LIVE);
+  };
+  __nv_bfloat16* const* w_peers = p.w_peers;
+  __nv_bfloat16* const* g_peers_rw = const_cast<__nv_bfloat16* const*>(p.g_peers);
 
-    if (UPDATE) {
-      const uint4 wnew = adam8(sc, p, i * 8, g);
-      if (MODE == 1) {
-        *reinterpret_cast<uint4*>(p.w_peers[p.rank] + elem) = wnew;
-      } else if (MODE == 2) {
-        multimem_st_16B(p.w_mc + elem, wnew);
-      } else {
+  if (MODE == 1 || !UPDATE) {
+    // one-shot (small replicated buckets) and the plain averaging all-reduce: one pass
+    constexpr int U = ar_unroll<WORLD, MODE>();
+    for (int64_t i0 = t0; i0 < nvec; i0 += stride * U) {
+      uint4 raw[U][NL];
+      bool act[U];
 #pragma unroll
-        for (int r = 0; r < WORLD; ++r) st_peer_16B(p.w_peers[(p.rank + r) % WORLD] + elem, wnew);
+      for (int u = 0; u < U; ++u) {
+        act[u] = selected(i0 + u * stride);
+        if (act[u]) load_vec<WORLD, MODE>(p, p.start + (first + i0 + u * stride) * 8, raw[u]);
       }
-    } else {
-      const uint4 gout = pack8(g);
-      if (MODE == 1) {
-        // one-shot plain all-reduce cannot be in place (peers still read our copy): result
-        // goes to the weight arena slot of the same offset
-        *reinterpret_cast<uint4*>(p.w_peers[p.rank] + elem) = gout;
-      } else if (MODE == 2) {
-        multimem_st_16B(const_cast<__nv_bfloat16*>(p.g_mc) + elem, gout);
-      } else {
 #pragma unroll
-        for (int r = 0; r < WORLD; ++r)
-          st_peer_16B(const_cast<__nv_bfloat16*>(p.g_peers[(p.rank + r) % WORLD]) + elem, gout);
+      for (int u = 0; u < U; ++u) {
+        if (!act[u]) continue;
+        const int64_t i = i0 + u * stride, elem = p.start + (first + i) * 8;
+        float g[8];
+        reduce_vec<WORLD, MODE>(p, raw[u], g);
+        if (UPDATE) {
+          AdamState8 as = adam_load8(p, i * 8);
+          store_all_ranks<WORLD, MODE>(p, w_peers, p.w_mc, elem, adam8(sc, p, i * 8, as, g));
+        } else {
+          // one-shot plain all-reduce cannot be in place (peers still read our copy): its result goes to
+          // the weight arena slot of the same offset
+          store_all_ranks<WORLD, MODE>(p, MODE == 1 ? w_peers : g_peers_rw,
+                                       const_cast<__nv_bfloat16*>(p.g_mc), elem, pack8(g));
+        }
+      }
+    }
+  } else {
+    // Sharded optimizer (two-shot / NVLS), two passes of the same thread over the same vectors.
+    // Pass A, latency-bound on the switch: many peer loads in flight, the averaged gradient goes back (bf16)
+    // into this rank's own copy of its slice — no other rank reads that part of our arena.
+    // Pass B, HBM-bound: AdamW on the fp32 state, new bf16 weights to every rank.
+    // Splitting them keeps the register footprint small enough to co-reside with a GEMM CTA.
+    __nv_bfloat16* own_g = g_peers_rw[p.rank];
+    if (ROWS != ROWS_IDLE) {
+      constexpr int U = ar_unroll<WORLD, MODE>();
+      for (int64_t i0 = t0; i0 < nvec; i0 += stride * U) {
+        uint4 raw[U][NL];
+        bool act[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          act[u] = selected(i0 + u * stride);
+          if (act[u]) load_vec<WORLD, MODE>(p, p.start + (first + i0 + u * stride) * 8, raw[u]);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          if (!act[u]) continue;
+          float g[8];
+          reduce_vec<WORLD, MODE>(p, raw[u], g);
+          *reinterpret_cast<uint4*>(own_g + p.start + (first + i0 + u * stride) * 8) = pack8(g);
+        }
+      }
+    }
+    constexpr int UB = AR_UPDATE_UNROLL;
+    for (int64_t i0 = t0; i0 < nvec; i0 += stride * UB) {
+      uint4 gv[UB];
+      AdamState8 as[UB];
+      bool act[UB];
+#pragma unroll
+      for (int u = 0; u < UB; ++u) {
+        const int64_t i = i0 + u * stride;
+        act[u] = selected(i);
+        if (!act[u]) continue;
+        if (ROWS != ROWS_IDLE) gv[u] = *reinterpret_cast<const uint4*>(own_g + p.start + (first + i) * 8);
+        as[u] = adam_load8(p, i * 8);
+      }
+#pragma unroll
+      for (int u = 0; u < UB; ++u) {
+        if (!act[u]) continue;
+        const int64_t i = i0 + u * stride;
+        float g[8];
+        if (ROWS == ROWS_IDLE) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) g[j] = 0.f;
+        } else {
+          unpack8(gv[u], g);
+        }
+        store_all_ranks<WORLD, MODE>(p, w_peers, p.w_mc, p.start + (first + i) * 8, adam8(sc, p, i * 8, as[u], g));
       }
     }
   }
@@ -243,7 +348,7 @@ __device__ __forceinline__ void allreduce_block(const ArKernelParams& p, int blo
 }
 
 template <int WORLD, int MODE, bool UPDATE, int ROWS>
-__global__ void __launch_bounds__(AR_THREADS) fused_allreduce_kernel(const ArKernelParams p) {
+__global__ void __launch_bounds__(AR_THREADS, AR_MIN_BLOCKS_PER_SM) fused_allreduce_kernel(const ArKernelParams p) {
   allreduce_block<WORLD, MODE, UPDATE, ROWS>(p, blockIdx.x, gridDim.x);
 }
 
@@ -259,7 +364,7 @@ struct ArEmuParams {
   int blocks;
 };
 template <int WORLD, int MODE, bool UPDATE, int ROWS>
-__global__ void __launch_bounds__(AR_THREADS) fused_allreduce_emulated_kernel(const __grid_constant__ ArEmuParams ep) {
+__global__ void __launch_bounds__(AR_THREADS, AR_MIN_BLOCKS_PER_SM) fused_allreduce_emulated_kernel(const __grid_constant__ ArEmuParams ep) {
   const int rank = blockIdx.x / ep.blocks, block = blockIdx.x % ep.blocks;
   ArKernelParams p = ep.base;
   p.rank = rank;
@@ -305,10 +410,10 @@ __device__ __forceinline__ void mark_rows_block(const ArKernelParams& p, int blo
   block_barrier(p, block, 2 * e + 2);
   if (threadIdx.x == 0) p.epoch[block] = e + 1;
 }
-__global__ void __launch_bounds__(AR_THREADS) mark_rows_kernel(const ArKernelParams p) {
+__global__ void __launch_bounds__(AR_THREADS, AR_MIN_BLOCKS_PER_SM) mark_rows_kernel(const ArKernelParams p) {
   mark_rows_block(p, blockIdx.x, gridDim.x);
 }
-__global__ void __launch_bounds__(AR_THREADS) mark_rows_emulated_kernel(const __grid_constant__ ArEmuParams ep) {
+__global__ void __launch_bounds__(AR_THREADS, AR_MIN_BLOCKS_PER_SM) mark_rows_emulated_kernel(const __grid_constant__ ArEmuParams ep) {
   const int rank = blockIdx.x / ep.blocks, block = blockIdx.x % ep.blocks;
   ArKernelParams p = ep.base;
   p.rank = rank;
@@ -321,14 +426,15 @@ __global__ void __launch_bounds__(AR_THREADS) mark_rows_emulated_kernel(const __
 }
 
 // world == 1 or "my optimizer is local" case on IPC arenas: AdamW over owned vectors only.
-__global__ void __launch_bounds__(AR_THREADS) local_update_kernel(const ArKernelParams p) {
+__global__ void __launch_bounds__(AR_THREADS, AR_MIN_BLOCKS_PER_SM) local_update_kernel(const ArKernelParams p) {
   const AdamScalars sc = load_adam_scalars(p.st);
   const int64_t nvec = p.numel / 8;
   for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < nvec; i += int64_t(gridDim.x) * blockDim.x) {
     const int64_t elem = p.start + i * 8;
     float g[8];
     unpack8(*reinterpret_cast<const uint4*>(p.g_peers[p.rank] + elem), g);
-    *reinterpret_cast<uint4*>(p.w_peers[p.rank] + elem) = adam8(sc, p, i * 8, g);
+    AdamState8 as = adam_load8(p, i * 8);
+    *reinterpret_cast<uint4*>(p.w_peers[p.rank] + elem) = adam8(sc, p, i * 8, as, g);
   }
 }
 

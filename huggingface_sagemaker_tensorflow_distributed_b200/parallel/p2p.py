@@ -154,9 +154,9 @@ class P2PGroup:
         self.world, self.rank, self.device = comm.size(), comm.rank(), device
         self.total, self.buckets = total_elems, buckets
         self.max_blocks = lib.hstd_allreduce_max_blocks()
-        # Blocks per bucket kernel.  Buckets that run underneath backward share the SMs with the GEMMs and are
-        # sized small; the trailing bucket(s) have no compute left to protect and take the whole budget.
-        self.blocks = blocks or int(os.environ.get("HSTD_AR_BLOCKS", "32"))
+        # Blocks (of 128 threads, small enough to sit next to a GEMM CTA on the same SM) per bucket kernel.
+        # The trailing bucket(s) have no compute left to protect and take the whole budget.
+        self.blocks = blocks or int(os.environ.get("HSTD_AR_BLOCKS", "96"))
         self.tail_blocks = int(os.environ.get("HSTD_AR_TAIL_BLOCKS", str(self.max_blocks)))
         w_bytes = _align(total_elems * 2, 256)
         # flag slots: one per bucket, one spare (collective tests / sweeps), one for the sparse-row marking
@@ -342,7 +342,7 @@ class P2PGroup:
         local = getattr(self, "debug_no_comm", False)
         mode = self.modes[b.index]
         start_o, n_o, off = self.owned[b.index]
-        mark = self.make_args(self.mark_slot, b.start, b.numel, mode, False, state, blocks=16,
+        mark = self.make_args(self.mark_slot, b.start, b.numel, mode, False, state, blocks=32,
                               world=1 if local else None)
         mark.n_ids = n_ids
         if local:

