@@ -38,6 +38,8 @@ def parse(argv=None):
     ap.add_argument("--no_graph", action="store_true")
     ap.add_argument("--dropout", type=float, default=None)
     ap.add_argument("--exposed_comm", action="store_true", help="also time a no-communication step")
+    ap.add_argument("--timeline", default=None, help="after the timed runs: write a per-kernel timeline (start, "
+                    "duration, stream) of one replayed step on rank 0 to this file (CUPTI via torch.profiler)")
     return ap.parse_args(argv)
 
 
@@ -178,6 +180,10 @@ def main() -> None:
             eng._run(plan)
         torch.cuda.synchronize()
         clocks = sampler.stop()
+        if a.timeline:
+            from huggingface_sagemaker_tensorflow_distributed_b200.utils.timers import kernel_timeline
+
+            kernel_timeline(lambda: eng._run(plan), a.timeline if rank == 0 else None, steps=4)
         launches = plan.launches * K
         parallelism = f"dp{world}" + ("" if world == 1 else f"-{eng.dp.mode}")
         extra["dp"] = eng.dp.describe() if world > 1 else {"mode": "local"}

@@ -53,6 +53,8 @@ struct ArKernelParams {
   int world, rank;
   int flag_slot;  // first flag slot of this bucket: flags[(flag_slot + block) * AR_MAX_WORLD + rank]
   int mode;       // hstd_ar_mode
+  int phase;      // 0: reduce + update in one launch, 1: reduce only, 2: update only (see allreduce_block)
+  int sync;       // bit 0: flag barrier before the work, bit 1: flag barrier after it
   float inv_world;
   // Row-sparse buckets (the embedding tables): the bucket is a stack of rows of `row_elems` elements and
   // `row_stamp[row] == stamp` marks the rows that received a gradient on ANY rank in this step.
@@ -144,9 +146,11 @@ struct AdamState8 {
 };
 __device__ __forceinline__ AdamState8 adam_load8(const ArKernelParams& p, int64_t o) {
   AdamState8 s;
-  s.w0 = *reinterpret_cast<const float4*>(p.master + o); s.w1 = *reinterpret_cast<const float4*>(p.master + o + 4);
-  s.m0 = *reinterpret_cast<const float4*>(p.m + o); s.m1 = *reinterpret_cast<const float4*>(p.m + o + 4);
-  s.v0 = *reinterpret_cast<const float4*>(p.v + o); s.v1 = *reinterpret_cast<const float4*>(p.v + o + 4);
+  // streaming (evict-first) accesses: 24 bytes of state per parameter pass through once per step and must
+  // not push the activations and weights of the concurrently running backward out of L2
+  s.w0 = __ldcs(reinterpret_cast<const float4*>(p.master + o)); s.w1 = __ldcs(reinterpret_cast<const float4*>(p.master + o + 4));
+  s.m0 = __ldcs(reinterpret_cast<const float4*>(p.m + o)); s.m1 = __ldcs(reinterpret_cast<const float4*>(p.m + o + 4));
+  s.v0 = __ldcs(reinterpret_cast<const float4*>(p.v + o)); s.v1 = __ldcs(reinterpret_cast<const float4*>(p.v + o + 4));
   return s;
 }
 // AdamW on those 8 elements; stores the new state and returns the new bf16 weights.
@@ -156,9 +160,9 @@ __device__ __forceinline__ uint4 adam8(const AdamScalars& sc, const ArKernelPara
   adam_update(sc, g[2], s.w0.z, s.m0.z, s.v0.z); adam_update(sc, g[3], s.w0.w, s.m0.w, s.v0.w);
   adam_update(sc, g[4], s.w1.x, s.m1.x, s.v1.x); adam_update(sc, g[5], s.w1.y, s.m1.y, s.v1.y);
   adam_update(sc, g[6], s.w1.z, s.m1.z, s.v1.z); adam_update(sc, g[7], s.w1.w, s.m1.w, s.v1.w);
-  *reinterpret_cast<float4*>(p.master + o) = s.w0; *reinterpret_cast<float4*>(p.master + o + 4) = s.w1;
-  *reinterpret_cast<float4*>(p.m + o) = s.m0; *reinterpret_cast<float4*>(p.m + o + 4) = s.m1;
-  *reinterpret_cast<float4*>(p.v + o) = s.v0; *reinterpret_cast<float4*>(p.v + o + 4) = s.v1;
+  __stcs(reinterpret_cast<float4*>(p.master + o), s.w0); __stcs(reinterpret_cast<float4*>(p.master + o + 4), s.w1);
+  __stcs(reinterpret_cast<float4*>(p.m + o), s.m0); __stcs(reinterpret_cast<float4*>(p.m + o + 4), s.m1);
+  __stcs(reinterpret_cast<float4*>(p.v + o), s.v0); __stcs(reinterpret_cast<float4*>(p.v + o + 4), s.v1);
   const float w[8] = {s.w0.x, s.w0.y, s.w0.z, s.w0.w, s.w1.x, s.w1.y, s.w1.z, s.w1.w};
   return pack8(w);
 }
@@ -221,19 +225,30 @@ __device__ __forceinline__ void store_all_ranks(const ArKernelParams& p, __nv_bf
 //                   read from any peer and no rank has to be waited for — m and v decay, the weight takes
 //                   its (history-driven) Adam step, the new bf16 row goes to every rank.  No rank reads an
 //                   idle embedding row during the step, so this part runs under the forward pass.
-enum { ROWS_ALL = 0, ROWS_LIVE = 1, ROWS_IDLE = 2 };
+//   ROWS_BOTH     : (update-only launches) every row; live rows take the reduced gradient, idle rows zero.
+enum { ROWS_ALL = 0, ROWS_LIVE = 1, ROWS_IDLE = 2, ROWS_BOTH = 3 };
 
 // The work of one block of one rank.  `block` / `nblocks` are passed in (not blockIdx / gridDim) so the
 // single-GPU emulation below can run several ranks inside one cooperative grid.
 // MODE: 0 two-shot, 1 one-shot, 2 NVLS.  UPDATE: fused AdamW (true) or plain averaged all-reduce written
 // back into every rank's gradient arena (false; used by the bandwidth sweep and the collective tests).
+// Sharded (two-shot / NVLS) optimizer launches come in three forms (p.phase):
+//   0  reduce + update of the bucket in one launch (barrier | reduce | AdamW + weight broadcast | barrier);
+//   1  reduce only: barrier, then the averaged gradient of this rank's slice is written back (bf16) into the
+//      rank's OWN copy of that slice.  Little HBM traffic (2 B/param), so these run underneath backward
+//      without fighting the GEMMs for bandwidth;
+//   2  update only: AdamW over the slice from those averaged gradients + weight broadcast, launched for all
+//      buckets at the end of the step with big blocks at full HBM speed.  (An HBM-bound kernel at full
+//      bandwidth needs most of an SM's registers for requests in flight: measured, hiding AdamW underneath
+//      backward in small co-resident blocks cost more through contention than it saved.)  By then every
+//      rank has finished backward, so no start barrier; the last launch of the step carries the end barrier.
 template <int WORLD, int MODE, bool UPDATE, int ROWS>
 __device__ __forceinline__ void allreduce_block(const ArKernelParams& p, int block, int nblocks) {
   if (already_failed(p)) return;
-  const uint32_t e = p.epoch[block];
-  if (ROWS != ROWS_IDLE) {
+  uint32_t e = p.epoch[block];
+  if (p.sync & 1) {
     // every rank's gradients of this bucket are complete
-    if (!block_barrier(p, block, 2 * e + 1)) return;  // a peer is gone: leave weights and optimizer state alone
+    if (!block_barrier(p, block, ++e)) return;  // a peer is gone: leave weights and optimizer state alone
   }
   AdamScalars sc;
   uint32_t stamp = 0;
@@ -249,11 +264,13 @@ __device__ __forceinline__ void allreduce_block(const ArKernelParams& p, int blo
 
   constexpr int NL = MODE == 2 ? 1 : WORLD;  // 16-byte loads per vector
   const int64_t t0 = block * int64_t(blockDim.x) + threadIdx.x;
+  auto row_live = [&](int64_t i) -> bool {
+    return p.row_stamp[uint32_t(p.row_vec0 + first + i) / row_vecs] == stamp;
+  };
   auto selected = [&](int64_t i) -> bool {
     if (i >= nvec) return false;
-    if (ROWS == ROWS_ALL) return true;
-    const bool live = p.row_stamp[uint32_t(p.row_vec0 + first + i) / row_vecs] == stamp;
-    return live == (ROWS == ROWS_LIVE);
+    if (ROWS == ROWS_ALL || ROWS == ROWS_BOTH) return true;
+    return row_live(i) == (ROWS == ROWS_LIVE);
   };
   __nv_bfloat16* const* w_peers = p.w_peers;
   __nv_bfloat16* const* g_peers_rw = const_cast<__nv_bfloat16* const*>(p.g_peers);
@@ -293,7 +310,7 @@ __device__ __forceinline__ void allreduce_block(const ArKernelParams& p, int blo
     // Pass B, HBM-bound: AdamW on the fp32 state, new bf16 weights to every rank.
     // Splitting them keeps the register footprint small enough to co-reside with a GEMM CTA.
     __nv_bfloat16* own_g = g_peers_rw[p.rank];
-    if (ROWS != ROWS_IDLE) {
+    if (ROWS != ROWS_IDLE && ROWS != ROWS_BOTH && p.phase != 2) {
       constexpr int U = ar_unroll<WORLD, MODE>();
       for (int64_t i0 = t0; i0 < nvec; i0 += stride * U) {
         uint4 raw[U][NL];
@@ -313,7 +330,7 @@ __device__ __forceinline__ void allreduce_block(const ArKernelParams& p, int blo
       }
     }
     constexpr int UB = AR_UPDATE_UNROLL;
-    for (int64_t i0 = t0; i0 < nvec; i0 += stride * UB) {
+    for (int64_t i0 = t0; i0 < nvec && p.phase != 1; i0 += stride * UB) {
       uint4 gv[UB];
       AdamState8 as[UB];
       bool act[UB];
@@ -322,7 +339,9 @@ __device__ __forceinline__ void allreduce_block(const ArKernelParams& p, int blo
         const int64_t i = i0 + u * stride;
         act[u] = selected(i);
         if (!act[u]) continue;
-        if (ROWS != ROWS_IDLE) gv[u] = *reinterpret_cast<const uint4*>(own_g + p.start + (first + i) * 8);
+        gv[u] = make_uint4(0, 0, 0, 0);  // (bf16 zeros) idle rows: the gradient is zero on every rank
+        if (ROWS == ROWS_ALL || ROWS == ROWS_LIVE || (ROWS == ROWS_BOTH && row_live(i)))
+          gv[u] = *reinterpret_cast<const uint4*>(own_g + p.start + (first + i) * 8);
         as[u] = adam_load8(p, i * 8);
       }
 #pragma unroll
@@ -330,25 +349,23 @@ __device__ __forceinline__ void allreduce_block(const ArKernelParams& p, int blo
         if (!act[u]) continue;
         const int64_t i = i0 + u * stride;
         float g[8];
-        if (ROWS == ROWS_IDLE) {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) g[j] = 0.f;
-        } else {
-          unpack8(gv[u], g);
-        }
+        unpack8(gv[u], g);
         store_all_ranks<WORLD, MODE>(p, w_peers, p.w_mc, p.start + (first + i) * 8, adam8(sc, p, i * 8, as[u], g));
       }
     }
   }
 
-  if (ROWS != ROWS_IDLE) {
-    block_barrier(p, block, 2 * e + 2);  // all peers finished reading our gradients / writing our weights
-    if (threadIdx.x == 0) p.epoch[block] = e + 1;
-  }
+  if (p.sync & 2) block_barrier(p, block, ++e);  // all peers finished reading our gradients / writing our weights
+  if ((p.sync & 3) && threadIdx.x == 0) p.epoch[block] = e;
 }
 
-template <int WORLD, int MODE, bool UPDATE, int ROWS>
-__global__ void __launch_bounds__(AR_THREADS, AR_MIN_BLOCKS_PER_SM) fused_allreduce_kernel(const ArKernelParams p) {
+// THREADS = AR_THREADS: the co-resident form for buckets that run underneath backward.  THREADS = AR_TAIL_THREADS:
+// the trailing buckets of a step have no compute kernel left to share the SM with and both passes are bound by
+// the number of requests in flight, so they take four times the threads (and the registers that go with them).
+constexpr int AR_TAIL_THREADS = 512;
+template <int WORLD, int MODE, bool UPDATE, int ROWS, int THREADS>
+__global__ void __launch_bounds__(THREADS, THREADS == AR_THREADS ? AR_MIN_BLOCKS_PER_SM : 1)
+fused_allreduce_kernel(const ArKernelParams p) {
   allreduce_block<WORLD, MODE, UPDATE, ROWS>(p, blockIdx.x, gridDim.x);
 }
 
@@ -438,26 +455,32 @@ __global__ void __launch_bounds__(AR_THREADS, AR_MIN_BLOCKS_PER_SM) local_update
   }
 }
 
-template <int MODE, bool UPDATE, int ROWS>
+template <int MODE, bool UPDATE, int ROWS, int THREADS>
 static int launch_world(const ArKernelParams& p, int blocks, cudaStream_t s) {
   switch (p.world) {
     case 1:  // a rank on its own: the row-sparse optimizer without peers (timing aid, single-GPU sparse update)
       if (MODE != 0 || !UPDATE) return set_error(-1, "allreduce: world 1 exists for the two-shot optimizer form only");
-      fused_allreduce_kernel<1, 0, true, ROWS><<<blocks, AR_THREADS, 0, s>>>(p);
+      fused_allreduce_kernel<1, 0, true, ROWS, THREADS><<<blocks, THREADS, 0, s>>>(p);
       break;
-    case 2: fused_allreduce_kernel<2, MODE, UPDATE, ROWS><<<blocks, AR_THREADS, 0, s>>>(p); break;
-    case 4: fused_allreduce_kernel<4, MODE, UPDATE, ROWS><<<blocks, AR_THREADS, 0, s>>>(p); break;
-    case 8: fused_allreduce_kernel<8, MODE, UPDATE, ROWS><<<blocks, AR_THREADS, 0, s>>>(p); break;
+    case 2: fused_allreduce_kernel<2, MODE, UPDATE, ROWS, THREADS><<<blocks, THREADS, 0, s>>>(p); break;
+    case 4: fused_allreduce_kernel<4, MODE, UPDATE, ROWS, THREADS><<<blocks, THREADS, 0, s>>>(p); break;
+    case 8: fused_allreduce_kernel<8, MODE, UPDATE, ROWS, THREADS><<<blocks, THREADS, 0, s>>>(p); break;
     default: return set_error(-1, "allreduce: world size must be 2, 4 or 8");
   }
   return check_launch("fused_allreduce");
 }
-template <int MODE, bool UPDATE>
-static int launch_rows(const ArKernelParams& p, int rows, int blocks, cudaStream_t s) {
+// sharded optimizer form: row filter x (co-resident | tail) block size
+template <int MODE>
+static int launch_update(const ArKernelParams& p, int rows, bool tail, int blocks, cudaStream_t s) {
   switch (rows) {
-    case ROWS_ALL: return launch_world<MODE, UPDATE, ROWS_ALL>(p, blocks, s);
-    case ROWS_LIVE: return launch_world<MODE, UPDATE, ROWS_LIVE>(p, blocks, s);
-    case ROWS_IDLE: return launch_world<MODE, UPDATE, ROWS_IDLE>(p, blocks, s);
+    case ROWS_ALL:
+      return tail ? launch_world<MODE, true, ROWS_ALL, AR_TAIL_THREADS>(p, blocks, s)
+                  : launch_world<MODE, true, ROWS_ALL, AR_THREADS>(p, blocks, s);
+    case ROWS_LIVE:
+      return tail ? launch_world<MODE, true, ROWS_LIVE, AR_TAIL_THREADS>(p, blocks, s)
+                  : launch_world<MODE, true, ROWS_LIVE, AR_THREADS>(p, blocks, s);
+    case ROWS_IDLE: return launch_world<MODE, true, ROWS_IDLE, AR_THREADS>(p, blocks, s);
+    case ROWS_BOTH: return launch_world<MODE, true, ROWS_BOTH, AR_TAIL_THREADS>(p, blocks, s);
     default: return set_error(-1, "allreduce: unknown row filter");
   }
 }
@@ -513,6 +536,10 @@ static int fill_params(const hstd_allreduce_args* a, ArKernelParams& p) {
   p.world = a->world; p.rank = a->rank;
   p.flag_slot = a->bucket_index * AR_MAX_BLOCKS;
   p.mode = a->mode;
+  p.phase = a->phase;
+  // barriers: both for the one-launch form (none when only idle rows are touched), before a reduce-only launch,
+  // after an update-only launch only where the caller asks for it (the last one of the step)
+  p.sync = a->phase == 1 ? 1 : (a->phase == 2 ? (a->end_barrier ? 2 : 0) : (a->rows == HSTD_AR_ROWS_IDLE ? 0 : 3));
   p.inv_world = 1.0f / float(a->world);
   p.row_stamp = static_cast<const uint32_t*>(a->row_stamp);
   p.row_elems = a->row_elems;
@@ -523,7 +550,10 @@ static int fill_params(const hstd_allreduce_args* a, ArKernelParams& p) {
 
 static int check_rows(const hstd_allreduce_args* a) {
   if (a->rows == HSTD_AR_ROWS_ALL) return 0;
-  if (a->rows != HSTD_AR_ROWS_LIVE && a->rows != HSTD_AR_ROWS_IDLE) return set_error(-1, "allreduce: unknown row filter");
+  if (a->rows != HSTD_AR_ROWS_LIVE && a->rows != HSTD_AR_ROWS_IDLE && a->rows != HSTD_AR_ROWS_BOTH)
+    return set_error(-1, "allreduce: unknown row filter");
+  if (a->rows == HSTD_AR_ROWS_BOTH && a->phase != 2)
+    return set_error(-1, "allreduce: HSTD_AR_ROWS_BOTH belongs to update-only launches (phase 2)");
   if (!a->update) return set_error(-1, "allreduce: row filters exist for the fused optimizer form only");
   if (!a->row_stamp || a->row_elems <= 0 || a->row_elems % 8 != 0)
     return set_error(-1, "allreduce: row filter needs row_stamp and row_elems (multiple of 8)");
@@ -559,13 +589,22 @@ extern "C" HSTD_API int hstd_fused_allreduce(const hstd_allreduce_args* a, void*
   if (update && (!a->master || !a->m || !a->v || !a->state)) return set_error(-1, "allreduce: optimizer state missing");
   if (a->mode == HSTD_AR_NVLS && (!a->g_mc || !a->w_mc)) return set_error(-1, "allreduce: NVLS needs multicast pointers");
   if (int rc = check_rows(a)) return rc;
+  if (a->phase < 0 || a->phase > 2) return set_error(-1, "allreduce: phase must be 0, 1 or 2");
+  if (a->phase != 0 && (!update || a->mode == HSTD_AR_ONE_SHOT))
+    return set_error(-1, "allreduce: split reduce / update launches exist for the sharded optimizer form only");
+  const bool tail = a->tail != 0;
   switch (a->mode) {
     case HSTD_AR_TWO_SHOT:
-      return update ? launch_rows<0, true>(p, a->rows, blocks, s) : launch_world<0, false, ROWS_ALL>(p, blocks, s);
+      if (update) return launch_update<0>(p, a->rows, tail, blocks, s);
+      return tail ? launch_world<0, false, ROWS_ALL, AR_TAIL_THREADS>(p, blocks, s)
+                  : launch_world<0, false, ROWS_ALL, AR_THREADS>(p, blocks, s);
     case HSTD_AR_ONE_SHOT:
-      return update ? launch_world<1, true, ROWS_ALL>(p, blocks, s) : launch_world<1, false, ROWS_ALL>(p, blocks, s);
+      return update ? launch_world<1, true, ROWS_ALL, AR_THREADS>(p, blocks, s)
+                    : launch_world<1, false, ROWS_ALL, AR_THREADS>(p, blocks, s);
     case HSTD_AR_NVLS:
-      return update ? launch_rows<2, true>(p, a->rows, blocks, s) : launch_world<2, false, ROWS_ALL>(p, blocks, s);
+      if (update) return launch_update<2>(p, a->rows, tail, blocks, s);
+      return tail ? launch_world<2, false, ROWS_ALL, AR_TAIL_THREADS>(p, blocks, s)
+                  : launch_world<2, false, ROWS_ALL, AR_THREADS>(p, blocks, s);
     default: return set_error(-1, "allreduce: unknown mode");
   }
 }
@@ -615,6 +654,7 @@ extern "C" HSTD_API int hstd_fused_allreduce_emulated(const hstd_allreduce_args*
     switch (a.rows) {
       case HSTD_AR_ROWS_LIVE: return launch_emulated_world<0, true, ROWS_LIVE>(ep, s);
       case HSTD_AR_ROWS_IDLE: return launch_emulated_world<0, true, ROWS_IDLE>(ep, s);
+      case HSTD_AR_ROWS_BOTH: return launch_emulated_world<0, true, ROWS_BOTH>(ep, s);
       default: return launch_emulated_world<0, true, ROWS_ALL>(ep, s);
     }
   }

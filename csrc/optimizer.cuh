@@ -16,7 +16,12 @@ __device__ __forceinline__ AdamScalars load_adam_scalars(const StepState* st) {
 __device__ __forceinline__ void adam_update(const AdamScalars& s, float g, float& w, float& m, float& v) {
   m = s.b1 * m + (1.f - s.b1) * g;
   v = s.b2 * v + (1.f - s.b2) * g * g;
-  w = w * s.decay - s.lr_t * m / (sqrtf(v) + s.eps);
+  // sqrt.approx / rcp.approx (1-2 ulp): the IEEE sqrt + divide sequences cost ~5x the instructions, which
+  // made the update pass of the fused all-reduce (few warps per SM, next to a GEMM CTA) compute-bound
+  float r, d;
+  asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(v));
+  asm("rcp.approx.f32 %0, %1;" : "=f"(d) : "f"(r + s.eps));
+  w = w * s.decay - s.lr_t * m * d;
 }
 
 }  // namespace hstd

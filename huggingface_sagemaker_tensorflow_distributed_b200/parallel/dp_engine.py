@@ -70,7 +70,15 @@ def plan_buckets_with_embeddings(slots, order: List[str], bucket_elems: int, wor
     emb = [n for n in order if n.startswith("emb.")]
     rest = [n for n in order if not n.startswith("emb.")]
     assert order[-len(emb):] == emb and emb[-1] == "emb.word.weight"
-    buckets = plan_buckets(slots, rest, bucket_elems, world)
+    # The gradients that complete last among the encoder's (layer 0: attention output + QKV projections) get a
+    # small bucket of their own: whatever is reduced after them is no longer hidden by compute, so the tail
+    # should not also carry the leftovers of the greedy packing.
+    last = [n for n in rest if n.startswith("layers.0.") and n.split(".")[2] in ("ln1", "out", "qkv")]
+    if last and rest[-len(last):] == last and len(rest) > len(last):
+        buckets = plan_buckets(slots, rest[:-len(last)], bucket_elems, world)
+        buckets.append(Bucket(len(buckets), slots[last[0]].offset, slots[last[-1]].end, last))
+    else:
+        buckets = plan_buckets(slots, rest, bucket_elems, world)
     word = slots["emb.word.weight"]
     d = word.shape[1]
     start, end = slots[emb[0]].offset, word.end
@@ -284,7 +292,7 @@ class DPEngine:
         assert self._tracker.done == len(self.buckets), "every bucket must be complete at end of backward"
         st = self.engine.state
         if self.p2p is not None and self.distributed:
-            self.p2p.record_end(plan)
+            self.p2p.record_end(plan, st, self.master, self.m, self.v, overlap=self.engine.overlap)
             return
         if self.mode == "p2p":
             raise NotImplementedError(

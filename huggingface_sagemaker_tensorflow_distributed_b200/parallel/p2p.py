@@ -38,10 +38,11 @@ class AllreduceArgs(C.Structure):
                 ("bucket_index", C.c_int32), ("mode", C.c_int32), ("update", C.c_int32), ("blocks", C.c_int32),
                 ("row_stamp", C.c_void_p), ("ids_peers", C.c_void_p * 8), ("row_elems", C.c_int32),
                 ("rows", C.c_int32), ("n_ids", C.c_int32), ("dense_rows", C.c_int32), ("vocab_rows", C.c_int32),
-                ("reserved_", C.c_int32), ("row_elem0", C.c_int64)]
+                ("tail", C.c_int32), ("row_elem0", C.c_int64),
+                ("phase", C.c_int32), ("end_barrier", C.c_int32)]
 
 
-ROWS_ALL, ROWS_LIVE, ROWS_IDLE = 0, 1, 2
+ROWS_ALL, ROWS_LIVE, ROWS_IDLE, ROWS_BOTH = 0, 1, 2, 3
 MAX_IDS_PER_RANK = 64 * 1024  # tokens of one step and rank the peer-visible id slot can hold
 
 
@@ -156,8 +157,10 @@ class P2PGroup:
         self.max_blocks = lib.hstd_allreduce_max_blocks()
         # Blocks (of 128 threads, small enough to sit next to a GEMM CTA on the same SM) per bucket kernel.
         # The trailing bucket(s) have no compute left to protect and take the whole budget.
-        self.blocks = blocks or int(os.environ.get("HSTD_AR_BLOCKS", "96"))
+        self.blocks = blocks or int(os.environ.get("HSTD_AR_BLOCKS", "128"))
         self.tail_blocks = int(os.environ.get("HSTD_AR_TAIL_BLOCKS", str(self.max_blocks)))
+        # split schedule: reduce underneath backward, AdamW of all buckets at full HBM speed at the end of the step
+        self.split = os.environ.get("HSTD_AR_SPLIT", "1") != "0"
         w_bytes = _align(total_elems * 2, 256)
         # flag slots: one per bucket, one spare (collective tests / sweeps), one for the sparse-row marking
         self.mark_slot = len(buckets) + 1
@@ -238,8 +241,10 @@ class P2PGroup:
 
     def make_args(self, bucket_index: int, start: int, numel: int, mode: int, update: bool, state=None, master=None,
                   m=None, v=None, owned_offset: int = 0, blocks: Optional[int] = None, rows: int = ROWS_ALL,
-                  world: Optional[int] = None, row_elem0: int = 0) -> AllreduceArgs:
+                  world: Optional[int] = None, row_elem0: int = 0, tail: bool = False, phase: int = 0,
+                  end_barrier: bool = False) -> AllreduceArgs:
         a = AllreduceArgs()
+        a.tail, a.phase, a.end_barrier = int(tail), phase, int(end_barrier)
         if rows != ROWS_ALL or bucket_index == self.mark_slot:
             sp = self.sparse
             a.row_stamp = self.row_stamp.data_ptr()
@@ -333,9 +338,10 @@ class P2PGroup:
         return fork
 
     def record_step_start(self, plan, state, master, m, v, n_ids: int) -> None:
-        """Row-sparse embedding bucket, start of the step (called right after the step prologue): mark the
-        rows that are live in this step, clear them in the local gradient arena, then give every idle row its
-        zero-gradient Adam step — all on the comm stream, underneath the forward pass."""
+        """Row-sparse embedding bucket, start of the step (called right after the step prologue), on the comm
+        stream underneath the forward pass: mark the rows that are live in this step and clear them in the
+        local gradient arena.  One-launch schedule (HSTD_AR_SPLIT=0) only: the idle rows also take their
+        zero-gradient Adam step here."""
         b = self.sparse
         if b is None:
             return
@@ -345,11 +351,13 @@ class P2PGroup:
         mark = self.make_args(self.mark_slot, b.start, b.numel, mode, False, state, blocks=32,
                               world=1 if local else None)
         mark.n_ids = n_ids
-        if local:
-            idle = self.make_args(b.index, start_o, n_o, AR_TWO_SHOT, True, state, master, m, v, off, rows=ROWS_IDLE,
-                                  world=1, row_elem0=start_o - b.start)
-        else:
-            idle = self.make_args(b.index, b.start, b.numel, mode, True, state, master, m, v, off, rows=ROWS_IDLE)
+        idle = None
+        if not self.split:
+            if local:
+                idle = self.make_args(b.index, start_o, n_o, AR_TWO_SHOT, True, state, master, m, v, off,
+                                      rows=ROWS_IDLE, world=1, row_elem0=start_o - b.start)
+            else:
+                idle = self.make_args(b.index, b.start, b.numel, mode, True, state, master, m, v, off, rows=ROWS_IDLE)
         fork = self._fork_to_comm(plan)
         ev_marked = torch.cuda.Event()
         plan.keep.append(ev_marked)
@@ -359,11 +367,12 @@ class P2PGroup:
             fork()
             self.launch_mark(mark, cs)
             ev_marked.record(cs)
-            self.launch(idle, cs)
+            if idle is not None:
+                self.launch(idle, cs)
 
-        plan.launches += 2
+        plan.launches += 1 + (idle is not None)
         plan.ops.append(op)
-        plan.names.append("sparse rows: mark + idle-row adamw@comm")
+        plan.names.append("sparse rows: mark" + (" + idle-row adamw" if idle is not None else "") + "@comm")
         plan.uses_comm_stream = True
         plan.rows_marked_event = ev_marked
 
@@ -377,24 +386,40 @@ class P2PGroup:
 
     def record_bucket(self, plan, bucket, state, master, m, v, overlap: bool = True, side_stream=None,
                       last: bool = False) -> None:
+        """Called when the gradients of ``bucket`` are complete.  Split schedule (default): a reduce-only launch
+        that runs underneath the rest of backward; the optimizer pass of every bucket follows at the end of the
+        step (record_end).  One-launch schedule: reduce + AdamW + weight broadcast here."""
         mode = self.modes[bucket.index]
         start_o, n_o, off = self.owned[bucket.index]
         sparse = getattr(bucket, "sparse", False)
         rows = ROWS_LIVE if sparse else ROWS_ALL
-        blocks = self.tail_blocks if (last or sparse) else self.blocks
-        if getattr(self, "debug_no_comm", False):
+        tail = last or sparse
+        blocks = self.tail_blocks if tail else self.blocks
+        local = getattr(self, "debug_no_comm", False)
+        split = self.split and mode != AR_ONE_SHOT
+        if split:
+            if not hasattr(plan, "pending_updates"):
+                plan.pending_updates = []
+            plan.pending_updates.append(bucket)
+            if local:
+                return  # exposed-communication timing: no reduce at all, the update pass reads the local gradients
+            args = self.make_args(bucket.index, bucket.start, bucket.numel, mode, True, state, master, m, v, off, blocks,
+                                  rows=rows, tail=tail, phase=1)
+            label = f"reduce[{MODE_NAMES[mode]}{',live rows' if sparse else ''}]"
+        elif local:
             # timing aid for the "exposed communication" metric: the same optimizer work on the
             # owned slice, but no peer traffic and no cross-rank flags (ranks diverge: never train so)
             if sparse:
                 args = self.make_args(bucket.index, start_o, n_o, AR_TWO_SHOT, True, state, master, m, v, off, blocks,
-                                      rows=ROWS_LIVE, world=1, row_elem0=start_o - bucket.start)
+                                      rows=ROWS_LIVE, world=1, row_elem0=start_o - bucket.start, tail=tail)
             else:
                 args = self.make_args(bucket.index, start_o, n_o, AR_LOCAL, True, state, master, m, v, off, blocks)
+            label = "adamw[local]"
         else:
             args = self.make_args(bucket.index, bucket.start, bucket.numel, mode, True, state, master, m, v, off, blocks,
-                                  rows=rows)
+                                  rows=rows, tail=tail)
+            label = f"allreduce+adamw[{MODE_NAMES[mode]}{',live rows' if sparse else ''}]"
         plan.launches += 1
-        label = f"allreduce+adamw[{MODE_NAMES[mode]}{',live rows' if sparse else ''}]"
         if not overlap:
             plan.ops.append(lambda args=args: self.launch(args))
             plan.names.append(label)
@@ -410,15 +435,48 @@ class P2PGroup:
         plan.names.append(label + "@comm")
         plan.uses_comm_stream = True
 
-    def record_end(self, plan) -> None:
+    def record_end(self, plan, state=None, master=None, m=None, v=None, overlap: bool = True) -> None:
+        """End of backward.  Split schedule: the optimizer pass of every sharded bucket, big blocks, back to back
+        behind the last reduce (whose barrier told us that every rank has finished backward, so peers' weights
+        may be overwritten); the last launch carries the step's closing barrier.  Then the main stream joins."""
+        pending = getattr(plan, "pending_updates", [])
+        local = getattr(self, "debug_no_comm", False)
+        cs = self.comm_stream if (overlap and getattr(plan, "uses_comm_stream", False)) else None
+        launches = []
+        for k, bucket in enumerate(pending):
+            mode = self.modes[bucket.index]
+            start_o, n_o, off = self.owned[bucket.index]
+            sparse = getattr(bucket, "sparse", False)
+            rows = ROWS_BOTH if sparse else ROWS_ALL
+            if local:
+                args = self.make_args(bucket.index, start_o, n_o, AR_TWO_SHOT, True, state, master, m, v, off,
+                                      self.tail_blocks, rows=rows, world=1, row_elem0=start_o - bucket.start, tail=True,
+                                      phase=2)
+            else:
+                args = self.make_args(bucket.index, bucket.start, bucket.numel, mode, True, state, master, m, v, off,
+                                      self.tail_blocks, rows=rows, tail=True, phase=2,
+                                      end_barrier=(k == len(pending) - 1))
+            launches.append(args)
+        if launches:
+            fork = self._fork_to_comm(plan) if (cs is not None and local) else None  # (no reduce launched a fork)
+
+            def run(launches=launches, fork=fork):
+                if fork is not None:
+                    fork()
+                for a in launches:
+                    self.launch(a, cs)
+
+            plan.launches += len(launches)
+            plan.ops.append(run)
+            plan.names.append(f"adamw + weight broadcast x{len(launches)}" + ("@comm" if cs is not None else ""))
         if not getattr(plan, "uses_comm_stream", False):
             return
         ev = torch.cuda.Event()
         plan.keep.append(ev)
-        cs = self.comm_stream
+        cs2 = self.comm_stream
 
         def op(ev=ev):
-            ev.record(cs)
+            ev.record(cs2)
             torch.cuda.current_stream().wait_event(ev)
 
         plan.ops.append(op)
@@ -427,6 +485,7 @@ class P2PGroup:
     def describe(self) -> Dict:
         return {"arena": self.arena.kind, "nvls": bool(self.arena.mc_ptr), "blocks": self.blocks,
                 "tail_blocks": self.tail_blocks,
+                "schedule": "reduce under backward, AdamW at step end" if self.split else "reduce+AdamW per bucket",
                 "buckets": [{"mb": round(b.numel * 2 / 2 ** 20, 2), "mode": MODE_NAMES[m],
                              **({"row_sparse": True} if getattr(b, "sparse", False) else {})}
                             for b, m in zip(self.buckets, self.modes)]}
@@ -457,8 +516,9 @@ class EmulatedP2P:
 
     def args(self, rank: int, bucket_index: int, start: int, numel: int, mode: int, update: bool, state=None,
              master=None, m=None, v=None, rows: int = ROWS_ALL, n_ids: int = 0, dense_rows: int = 0,
-             vocab_rows: int = 0) -> AllreduceArgs:
+             vocab_rows: int = 0, phase: int = 0, end_barrier: bool = False) -> AllreduceArgs:
         a = AllreduceArgs()
+        a.phase, a.end_barrier = phase, int(end_barrier)
         for r in range(self.world):
             a.w_peers[r], a.g_peers[r] = self.w16[r].data_ptr(), self.g16[r].data_ptr()
             a.flag_peers[r], a.ids_peers[r] = self.flags[r].data_ptr(), self.ids[r].data_ptr()

@@ -73,3 +73,43 @@ def profile_ops(ops: List[Callable[[], None]], names: List[str], repeats: int = 
     out = [(n, c // repeats, t / repeats) for n, (c, t) in acc.items()]
     out.sort(key=lambda x: -x[2])
     return out
+
+
+def kernel_timeline(step_fn, out_path, steps: int = 4) -> None:
+    """Runs ``steps`` steps under torch.profiler (CUPTI activity records; works for CUDA-graph replays and for
+    multi-rank jobs, where ncu cannot be used) and writes the kernels of the LAST step to ``out_path``:
+    start offset, duration, stream, name — plus per-stream busy time and the step's span.  Profiling adds
+    overhead; use the timeline for ordering / overlap / tails, not for absolute step time."""
+    import torch
+    from torch.profiler import ProfilerActivity, profile
+
+    torch.cuda.synchronize()
+    marks = []
+    with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
+        for _ in range(steps):
+            step_fn()
+            torch.cuda.synchronize()
+            marks.append(None)
+    if out_path is None:
+        return
+    raw = prof.profiler.kineto_results.events()
+    evs = [(e.start_ns() / 1e3, e.duration_ns() / 1e3, e.device_resource_id(), e.name()) for e in raw
+           if e.device_type() == torch.autograd.DeviceType.CUDA]
+    evs.sort()
+    if not evs:
+        with open(out_path, "w") as f:
+            f.write("no CUDA activity records (CUPTI unavailable?)\n")
+        return
+    # split into steps at the largest gaps between consecutive kernels (the host synchronises between steps)
+    gaps = sorted(range(1, len(evs)), key=lambda i: evs[i][0] - (evs[i - 1][0] + evs[i - 1][1]), reverse=True)
+    cut = max(gaps[:steps - 1]) if steps > 1 and len(gaps) >= steps - 1 else 0
+    last = evs[cut:]
+    t0 = last[0][0]
+    end = max(st + d for st, d, _, _ in last)
+    streams = {}
+    with open(out_path, "w") as f:
+        f.write(f"# kernels of one step: start_us  dur_us  stream  name   (span {end - t0:.1f} us, {len(last)} records)\n")
+        for st, d, sid, name in last:
+            streams[sid] = streams.get(sid, 0.0) + d
+            f.write(f"{st - t0:10.1f} {d:9.1f} {sid:>4d}  {name[:110]}\n")
+        f.write("# busy us per stream: " + ", ".join(f"{k}: {v:.0f}" for k, v in sorted(streams.items())) + "\n")

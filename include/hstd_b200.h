@@ -273,8 +273,12 @@ typedef struct hstd_allreduce_args {
   int32_t n_ids;       /* ids per rank */
   int32_t dense_rows;  /* leading rows of the bucket that are live in every step */
   int32_t vocab_rows;  /* rows addressable by an id, following the dense ones */
-  int32_t reserved_;
+  int32_t tail;        /* non-zero: nothing else runs on the GPU any more (last buckets of a step): use big blocks */
   int64_t row_elem0;   /* bucket-relative element offset of `start` when a launch covers part of a row-sparse bucket */
+  int32_t phase;       /* sharded optimizer form: 0 reduce + update in one launch; 1 reduce only (the averaged gradient
+                        * of this rank's slice is written back, bf16, into its own gradient arena); 2 update only
+                        * (AdamW from those averages + weight broadcast; no barrier before it) */
+  int32_t end_barrier; /* phase 2: finish with the cross-rank barrier (the last launch of a step must) */
 } hstd_allreduce_args;
 int hstd_fused_allreduce(const hstd_allreduce_args* args, void* stream);
 
@@ -292,7 +296,8 @@ int hstd_fused_allreduce(const hstd_allreduce_args* args, void* stream);
  *      path, under the forward pass (no rank reads an idle row during the step).
  *   3. hstd_fused_allreduce(rows = HSTD_AR_ROWS_LIVE) after backward: reduce + AdamW + broadcast of
  *      the live rows only.  Together 2 and 3 equal the dense update exactly. */
-enum { HSTD_AR_ROWS_ALL = 0, HSTD_AR_ROWS_LIVE = 1, HSTD_AR_ROWS_IDLE = 2 };
+enum { HSTD_AR_ROWS_ALL = 0, HSTD_AR_ROWS_LIVE = 1, HSTD_AR_ROWS_IDLE = 2,
+       HSTD_AR_ROWS_BOTH = 3 /* phase 2 only: live rows take the reduced gradient, idle rows zero */ };
 int hstd_sparse_rows_mark(const hstd_allreduce_args* args, void* stream);
 
 /* Single-GPU emulation of a `world`-rank launch for tests and profiling on a box with fewer GPUs

@@ -97,8 +97,9 @@ def check_collectives():
         log("OK fused_update", p2p.MODE_NAMES[mode])
 
 
-def check_row_sparse():
-    """mark -> idle rows -> live rows on real peers == dense reduce + AdamW (gathered fp32 reference)."""
+def check_row_sparse(split=False):
+    """one launch per part: mark -> idle rows -> live rows; split: mark -> reduce of live rows -> update of all rows.
+    On real peers, either == dense reduce + AdamW (gathered fp32 reference)."""
     W, R, dev = hvd.size(), hvd.rank(), comm.device()
     d, dense_rows, vocab, n_ids = 256, 6, 2000, 160
     rows = dense_rows + vocab
@@ -127,7 +128,8 @@ def check_row_sparse():
         mark = grp.make_args(grp.mark_slot, 0, total, mode, False, st, blocks=8)
         mark.n_ids = n_ids
         grp.launch_mark(mark)
-        grp.launch(grp.make_args(0, 0, total, mode, True, st, master, m, v, 0, rows=p2p.ROWS_IDLE))
+        if not split:
+            grp.launch(grp.make_args(0, 0, total, mode, True, st, master, m, v, 0, rows=p2p.ROWS_IDLE))
         gr = grp.g16.view(rows, d)
         torch.manual_seed(900 + 10 * step + R)
         gr[:dense_rows] = (torch.randn(dense_rows, d, device=dev) * 0.1).bfloat16()
@@ -142,7 +144,14 @@ def check_row_sparse():
         torch.cuda.synchronize()
         dist.barrier()
         avg = torch.stack(gather_all(mine)).sum(0).view(-1) / W
-        grp.launch(grp.make_args(0, 0, total, mode, True, st, master, m, v, 0, rows=p2p.ROWS_LIVE, blocks=grp.tail_blocks))
+        if split:
+            grp.launch(grp.make_args(0, 0, total, mode, True, st, master, m, v, 0, rows=p2p.ROWS_LIVE,
+                                     blocks=grp.tail_blocks, tail=True, phase=1))
+            grp.launch(grp.make_args(0, 0, total, mode, True, st, master, m, v, 0, rows=p2p.ROWS_BOTH,
+                                     blocks=grp.tail_blocks, tail=True, phase=2, end_barrier=True))
+        else:
+            grp.launch(grp.make_args(0, 0, total, mode, True, st, master, m, v, 0, rows=p2p.ROWS_LIVE,
+                                     blocks=grp.tail_blocks, tail=True))
         torch.cuda.synchronize()
         dist.barrier()
         K.adamw_flat(st, avg.bfloat16(), rm, rmm, rv, rw)  # the reduce pass hands a bf16 average to the optimizer pass
@@ -154,7 +163,7 @@ def check_row_sparse():
     same = gather_all(grp.w16)
     assert all(torch.equal(same[0], s) for s in same), "weights differ across ranks"
     assert (grp.w16.float() - rm).abs().max().item() <= 0.02 * rm.abs().max().item()
-    log("OK row_sparse", p2p.MODE_NAMES[mode])
+    log("OK row_sparse" + (" split" if split else ""), p2p.MODE_NAMES[mode])
 
 
 def _tiny_fit(samples, epochs=1, seed=5, on_step=None):
@@ -263,6 +272,7 @@ if __name__ == "__main__":
     if which in ("all", "collectives"):
         check_collectives()
         check_row_sparse()
+        check_row_sparse(split=True)
     if which == "uneven":
         check_uneven()
     if which == "dead_peer":

@@ -62,7 +62,12 @@ def test_plain_allreduce_and_fused_adamw(world, mode_name):
         avg = torch.stack([g.float() for g in emu.g16]).sum(0) / world
         K.step_prologue(sst, 1e-2, "constant", 0, 0, 0.9, 0.999, 1e-7, 0.01)
         for bi, (st, n) in enumerate(zip(starts, sizes)):
-            emu.allreduce([emu.args(r, bi, st, n, mode, True, sst, *state[r][bi]) for r in range(world)])
+            if mode == p2p.AR_TWO_SHOT and step == 1:  # the split schedule: reduce-only launch, update-only launch
+                emu.allreduce([emu.args(r, bi, st, n, mode, True, sst, *state[r][bi], phase=1) for r in range(world)])
+                emu.allreduce([emu.args(r, bi, st, n, mode, True, sst, *state[r][bi], phase=2, end_barrier=True)
+                               for r in range(world)])
+            else:
+                emu.allreduce([emu.args(r, bi, st, n, mode, True, sst, *state[r][bi]) for r in range(world)])
         torch.cuda.synchronize()
         # the sharded form hands the averaged gradient from its reduce pass to its optimizer pass in bf16
         _ref_adam(K.read_step_state(sst), avg if mode == p2p.AR_ONE_SHOT else avg.bfloat16().float(), rm, rmm, rv)
@@ -77,10 +82,12 @@ def test_plain_allreduce_and_fused_adamw(world, mode_name):
 
 
 @pytest.mark.parametrize("world", [2, 4, 8])
-def test_row_sparse_embedding_update_equals_the_dense_update(world):
-    """mark -> idle rows (zero-gradient Adam step, no reduction) -> live rows (reduce + AdamW) must leave
-    master / m / v / bf16 weights exactly where one dense reduce + AdamW over the whole table leaves them,
-    with gradient rows of earlier steps still lying around in the arena (they are never zeroed densely)."""
+@pytest.mark.parametrize("schedule", ["one_launch", "split"])
+def test_row_sparse_embedding_update_equals_the_dense_update(world, schedule):
+    """one_launch: mark -> idle rows (zero-gradient Adam step, no reduction) -> live rows (reduce + AdamW);
+    split: mark -> reduce of the live rows -> one update pass over all rows (live: reduced gradient, idle: zero).
+    Either must leave master / m / v / bf16 weights where one dense reduce + AdamW over the whole table leaves
+    them, with gradient rows of earlier steps still lying around in the arena (they are never zeroed densely)."""
     from huggingface_sagemaker_tensorflow_distributed_b200.ops import kernels as K
     from huggingface_sagemaker_tensorflow_distributed_b200.parallel import p2p
 
@@ -109,8 +116,9 @@ def test_row_sparse_embedding_update_equals_the_dense_update(world):
             emu.ids[r][:n_ids].copy_(ids[r])
         emu.mark([emu.args(r, emu.mark_slot, 0, total, p2p.AR_TWO_SHOT, False, sst, n_ids=n_ids, dense_rows=dense_rows,
                            vocab_rows=vocab) for r in range(world)])
-        emu.allreduce([emu.args(r, 0, 0, total, p2p.AR_TWO_SHOT, True, sst, *state[r], rows=p2p.ROWS_IDLE)
-                       for r in range(world)])
+        if schedule == "one_launch":
+            emu.allreduce([emu.args(r, 0, 0, total, p2p.AR_TWO_SHOT, True, sst, *state[r], rows=p2p.ROWS_IDLE)
+                           for r in range(world)])
         # "backward": dense rows are written in full, word rows are scatter-added into the cleared live rows
         dense_g = torch.zeros(world, rows, d, device=dev)
         for r in range(world):
@@ -124,8 +132,14 @@ def test_row_sparse_embedding_update_equals_the_dense_update(world):
             live = torch.unique(torch.cat(ids).long().to(dev)) + dense_rows
             assert torch.isfinite(gr[live].float()).all(), "a live row was not cleared by the marking kernel"
             dense_g[r, live] = gr[live].float()
-        emu.allreduce([emu.args(r, 0, 0, total, p2p.AR_TWO_SHOT, True, sst, *state[r], rows=p2p.ROWS_LIVE)
-                       for r in range(world)])
+        if schedule == "one_launch":
+            emu.allreduce([emu.args(r, 0, 0, total, p2p.AR_TWO_SHOT, True, sst, *state[r], rows=p2p.ROWS_LIVE)
+                           for r in range(world)])
+        else:
+            emu.allreduce([emu.args(r, 0, 0, total, p2p.AR_TWO_SHOT, True, sst, *state[r], rows=p2p.ROWS_LIVE, phase=1)
+                           for r in range(world)])
+            emu.allreduce([emu.args(r, 0, 0, total, p2p.AR_TWO_SHOT, True, sst, *state[r], rows=p2p.ROWS_BOTH, phase=2,
+                                    end_barrier=True) for r in range(world)])
         torch.cuda.synchronize()
         emu.check_errors()
         _ref_adam(K.read_step_state(sst), (dense_g.sum(0).view(-1) / world).bfloat16().float(), rm, rmm, rv)
