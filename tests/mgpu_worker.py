@@ -260,7 +260,11 @@ def check_training():
             assert model.backend.plans[(4, 128, True)].graph is not None
             p2p_flat = flat.clone()
         else:
-            assert (flat - p2p_flat).abs().max().item() < 5e-3, (flat - p2p_flat).abs().max().item()
+            # Elements whose gradient is rounding noise move by +-lr per step under Adam in either run, so the
+            # max-abs difference can approach the total movement (32 steps x 2e-4); the bulk must agree closely.
+            diff = flat - p2p_flat
+            assert diff.abs().max().item() < 1.3e-2, diff.abs().max().item()
+            assert (diff.norm() / flat.norm()).item() < 5e-3, (diff.norm() / flat.norm()).item()
     lp, ln = losses["p2p"], losses["nccl"]
     assert abs(lp[-1] - ln[-1]) < 2e-2, losses
     log("OK training p2p==nccl", lp, ln)

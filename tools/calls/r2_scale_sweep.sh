@@ -30,12 +30,12 @@ d=json.loads(sys.stdin.read())
 print('$label', d.get('ms_per_step'), 'ms', d.get('value'), 'samples/s exposed', d.get('exposed_comm_ms_per_step'), 'nocomm', d.get('no_comm_ms_per_step'))" 2>/dev/null || tail -3 gpurun_out/${TAG}_err.log
 }
 S="--steps 100 --warmup 8 --exposed_comm"
-run "mb16" HSTD_X=1 -- $S --bucket_mb 16 --timeline gpurun_out/${TAG}_timeline_n${N}.txt
-run "mb32" HSTD_X=1 -- $S --bucket_mb 32
-run "mb8" HSTD_X=1 -- $S --bucket_mb 8
-run "mb16-two_shot" HSTD_AR_MODE=two_shot -- $S --bucket_mb 16
-run "mb16-blocks64" HSTD_AR_BLOCKS=64 -- $S --bucket_mb 16
+run "mb32" HSTD_X=1 -- $S --bucket_mb 32 --timeline gpurun_out/${TAG}_timeline_n${N}.txt
+run "mb16" HSTD_X=1 -- $S --bucket_mb 16
+run "mb64" HSTD_X=1 -- $S --bucket_mb 64
+run "mb32-two_shot" HSTD_AR_MODE=two_shot -- $S --bucket_mb 32
+run "mb32-one-launch" HSTD_AR_SPLIT=0 -- $S --bucket_mb 32
 if [ "${MORE:-0}" = "1" ]; then
-  run "mb16-dense-emb" HSTD_SPARSE_EMB=0 -- $S --bucket_mb 16
-  run "mb32-two_shot" HSTD_AR_MODE=two_shot -- $S --bucket_mb 32
+  run "mb32-dense-emb" HSTD_SPARSE_EMB=0 -- $S --bucket_mb 32
+  run "mb32-blocks64" HSTD_AR_BLOCKS=64 -- $S --bucket_mb 32
 fi
