@@ -12,7 +12,7 @@ import torch.distributed as dist
 import torch.nn.functional as F
 
 
-def build(cfg, device, world: int, lr: float, sdpa: bool = True):
+def build(cfg, device, world: int, lr: float, sdpa: bool = True, capturable: bool = False):
     from huggingface_sagemaker_tensorflow_distributed_b200.models.reference import EncoderForSequenceClassification
 
     torch.manual_seed(42)
@@ -20,7 +20,7 @@ def build(cfg, device, world: int, lr: float, sdpa: bool = True):
     if world > 1:
         model = torch.nn.parallel.DistributedDataParallel(model, device_ids=[device.index], bucket_cap_mb=25,
                                                           gradient_as_bucket_view=True)
-    opt = torch.optim.AdamW(model.parameters(), lr=lr, eps=1e-7, weight_decay=0.0, fused=True)
+    opt = torch.optim.AdamW(model.parameters(), lr=lr, eps=1e-7, weight_decay=0.0, fused=True, capturable=capturable)
     return model, opt
 
 
@@ -32,3 +32,34 @@ def train_step(model, opt, ids, mask, labels):
     loss.backward()
     opt.step()
     return loss
+
+
+class GraphedStep:
+    """The same training step captured ONCE into a CUDA graph (forward, backward, DDP's NCCL all-reduces, fused
+    AdamW) and replayed: the library baseline without Python / launch latency, which is what a compiled TF graph
+    (``model.fit``, reference scripts/train.py:145) is the counterpart of.  Inputs are copied into static
+    tensors before each replay.  DDP asks for >= 11 eager iterations on a side stream before capture."""
+
+    def __init__(self, model, opt, ids, mask, labels, warmup: int = 12):
+        self.model, self.opt = model, opt
+        self.ids, self.mask, self.labels = ids.clone(), mask.clone(), labels.clone()
+        cur = torch.cuda.current_stream()
+        side = torch.cuda.Stream()
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):
+            for _ in range(warmup):
+                train_step(model, opt, self.ids, self.mask, self.labels)
+        cur.wait_stream(side)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        opt.zero_grad(set_to_none=True)
+        with torch.cuda.graph(self.graph):
+            self.loss = train_step(model, opt, self.ids, self.mask, self.labels)
+        torch.cuda.synchronize()
+
+    def __call__(self, ids, mask, labels):
+        self.ids.copy_(ids, non_blocking=True)
+        self.mask.copy_(mask, non_blocking=True)
+        self.labels.copy_(labels, non_blocking=True)
+        self.graph.replay()
+        return self.loss

@@ -38,6 +38,7 @@ def parse(argv=None):
     ap.add_argument("--no_graph", action="store_true")
     ap.add_argument("--dropout", type=float, default=None)
     ap.add_argument("--exposed_comm", action="store_true", help="also time a no-communication step")
+    ap.add_argument("--graph", action="store_true", help="--impl ddp: capture the whole DDP step in a CUDA graph")
     ap.add_argument("--timeline", default=None, help="after the timed runs: write a per-kernel timeline (start, "
                     "duration, stream) of one replayed step on rank 0 to this file (CUPTI via torch.profiler)")
     return ap.parse_args(argv)
@@ -128,28 +129,35 @@ def main() -> None:
         sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "baseline"))
         import ddp_baseline
 
-        model, opt = ddp_baseline.build(cfg, dev, world, lr)
+        model, opt = ddp_baseline.build(cfg, dev, world, lr, capturable=a.graph)
         dbatches = [(f["input_ids"].to(dev).long(), f["attention_mask"].to(dev), l.to(dev).long()) for f, l in batches]
+        step_fn = lambda *b: ddp_baseline.train_step(model, opt, *b)  # noqa: E731
+        if a.graph:
+            try:
+                step_fn = ddp_baseline.GraphedStep(model, opt, *dbatches[0])
+                extra["cuda_graph"] = True
+            except Exception as e:  # noqa: BLE001 - report and fall back to the eager arm
+                extra["cuda_graph"] = f"capture failed, eager used: {type(e).__name__}: {str(e)[:160]}"
+                torch.cuda.synchronize()
         for i in range(W):
-            ddp_baseline.train_step(model, opt, *dbatches[i % nb])
-        dev_ms, _ = timed(lambda i: ddp_baseline.train_step(model, opt, *dbatches[i % nb]), K)
+            step_fn(*dbatches[i % nb])
+        dev_ms, _ = timed(lambda i: step_fn(*dbatches[i % nb]), K)
 
         def e2e_step(i):
             f, l = batches[i % nb]
-            loss = ddp_baseline.train_step(model, opt, f["input_ids"].to(dev, non_blocking=True).long(),
-                                           f["attention_mask"].to(dev, non_blocking=True),
-                                           l.to(dev, non_blocking=True).long())
+            loss = step_fn(f["input_ids"].to(dev, non_blocking=True).long(),
+                           f["attention_mask"].to(dev, non_blocking=True), l.to(dev, non_blocking=True).long())
             loss.item()
 
         e2e_ms, _ = timed(e2e_step, K)
         # untimed: ~1.5 s more of the same load so the 100 ms clock sampler sees it.  The count is
         # derived from the all-reduced step time, hence identical on every rank.
         for _ in range(0 if os.environ.get("HSTD_BENCH_NO_COOLDOWN") else min(5000, int(1500.0 / max(dev_ms / K, 1e-3)) + 1)):
-            ddp_baseline.train_step(model, opt, *dbatches[0])
+            step_fn(*dbatches[0])
         torch.cuda.synchronize()
         clocks = sampler.stop()
         launches = None
-        parallelism = f"ddp{world}-nccl"
+        parallelism = f"ddp{world}-nccl" + ("-cudagraph" if extra.get("cuda_graph") is True else "")
     else:
         model = T.AutoModelForSequenceClassification.from_pretrained(
             a.model, device=dev, dropout=a.dropout, bucket_mb=a.bucket_mb, comm_mode=a.comm,

@@ -180,14 +180,17 @@ class P2PGroup:
         if force_mode is None and env_mode:
             force_mode = {"two_shot": AR_TWO_SHOT, "one_shot": AR_ONE_SHOT, "nvls": AR_NVLS}[env_mode]
         self.modes: List[int] = []
+        # Measured (profiles/scale_r2_n2.md): with two ranks the in-switch reduction has nothing to save — one
+        # peer load per vector either way — and plain peer loads / stores were faster (2.417 vs 2.436 ms/step).
+        nvls_pays = bool(self.arena.mc_ptr) and self.world > 2
         for b in buckets:
             if force_mode is not None:
                 mode = force_mode
             elif getattr(b, "sparse", False):  # sharded state is what the row filters work on
-                mode = AR_NVLS if self.arena.mc_ptr else AR_TWO_SHOT
+                mode = AR_NVLS if nvls_pays else AR_TWO_SHOT
             elif b.numel * 2 <= one_shot_bytes:
                 mode = AR_ONE_SHOT
-            elif self.arena.mc_ptr:
+            elif nvls_pays:
                 mode = AR_NVLS
             else:
                 mode = AR_TWO_SHOT
