@@ -408,20 +408,26 @@ __device__ __forceinline__ void mark_rows_block(const ArKernelParams& p, int blo
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, warps = blockDim.x >> 5;
   const int total = p.world * p.n_ids;
   const int row_vecs = p.row_elems / 8;
-  for (int t = block * warps + warp; t < total; t += nblocks * warps) {
-    const int src = t / p.n_ids, k = t - src * p.n_ids;
-    int id = 0;
+  // 32 ids per warp and round trip (one coalesced peer load; a load per id made this kernel latency-bound:
+  // 250 us at 4 ranks), then the warp walks through them and clears the rows it was first to stamp
+  for (int t0 = (block * warps + warp) * 32; t0 < total; t0 += nblocks * warps * 32) {
+    const int t = t0 + lane;
+    int id = -1;
     uint32_t old = stamp;
-    if (lane == 0) {
+    if (t < total) {
+      const int src = t / p.n_ids, k = t - src * p.n_ids;
       id = p.ids_peers[src][k];  // relaxed peer load; ordered after the barrier's acquire
       if (id >= 0 && id < p.vocab_rows) old = atomicExch(stamps + p.dense_rows + id, stamp);
     }
-    id = __shfl_sync(0xffffffffu, id, 0);
-    old = __shfl_sync(0xffffffffu, old, 0);
-    if (old == stamp) continue;  // somebody else got here first (or the id is out of range)
-    uint4* row = reinterpret_cast<uint4*>(const_cast<__nv_bfloat16*>(p.g_peers[p.rank]) + p.start +
-                                          int64_t(p.dense_rows + id) * p.row_elems);
-    for (int c = lane; c < row_vecs; c += 32) row[c] = make_uint4(0, 0, 0, 0);
+    uint32_t first = __ballot_sync(0xffffffffu, old != stamp);  // lanes whose row still has to be cleared
+    while (first) {
+      const int src_lane = __ffs(first) - 1;
+      first &= first - 1;
+      const int rid = __shfl_sync(0xffffffffu, id, src_lane);
+      uint4* row = reinterpret_cast<uint4*>(const_cast<__nv_bfloat16*>(p.g_peers[p.rank]) + p.start +
+                                            int64_t(p.dense_rows + rid) * p.row_elems);
+      for (int c = lane; c < row_vecs; c += 32) row[c] = make_uint4(0, 0, 0, 0);
+    }
   }
   // peers have finished reading our ids: the host may stage the next step's batch once this step is over
   block_barrier(p, block, 2 * e + 2);

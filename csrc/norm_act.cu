@@ -104,114 +104,150 @@ __global__ void __launch_bounds__(LN_WARPS * 32) ln_fwd_kernel(const hstd_ln_arg
 }
 
 // ------------------------------------------------------------------ LayerNorm backward
-// Two passes over the same (L2-resident) data instead of one register-heavy kernel:
-//   rows kernel: one warp per row, dpre = LN'(dropout_out'(dy)), da = dropout_in'(dpre);
-//   cols kernel: threads own 8 columns and walk the rows: dgamma, dbeta, dbias partials.
-// (A single fused kernel needs 72 column accumulators per lane on top of the row data: 201
-// registers -> 8 warps per SM and 1.3 TB/s; the split runs both halves at high occupancy.)
-template <int NV>
-__global__ void __launch_bounds__(LN_WARPS * 32) ln_bwd_rows_kernel(const hstd_ln_bwd_args p) {
+// ONE kernel: dpre = LN'(dropout_out'(dy)), da = dropout_in'(dpre) row by row (one warp per row, 16-byte
+// vectors, warp-shuffle statistics) AND the three column reductions dgamma = sum dy*xhat, dbeta = sum dy,
+// dbias = sum da.  A warp cannot keep 3 x d/32 column accumulators in registers next to its row data (that
+// version needed 201 registers), so every warp adds its rows' contributions into a private fp32 slice of
+// shared memory (conflict-free float4 layout), the block folds its slices, and the block sums go to a small
+// fp32 accumulator in global memory with vector reductions (red.global.add.v4.f32).  The last block to finish
+// converts the accumulator to the bf16 gradients and leaves it zeroed for the next call — no partials round
+// trip, no finalize launch.  (Round 1 ran rows / columns / finalize as three kernels: 21.7 us per LayerNorm,
+// reading dy, pre and da twice.)
+// `partials` (args): LN_BWD_ACC_FLOATS fp32 + one counter word, zero before the first call.
+constexpr int LN_BWD_ACC_FLOATS = 3 * 1024;
+constexpr int LN_BWD_ROWS = 2;  // rows per warp
+
+__device__ __forceinline__ void red_add_v4(float* addr, const float4& v) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
+
+template <int NV, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32) ln_bwd_fused_kernel(const hstd_ln_bwd_args p) {
+  extern __shared__ float4 ln_sm[];  // [WARPS][3][NV*64] float4, position q = (i*2 + half)*32 + lane
   HSTD_PDL_PROLOGUE();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int row = blockIdx.x * LN_WARPS + warp;
-  if (row >= p.M) return;
   const int d = p.d;
+  constexpr int Q = NV * 64;  // float4 positions per quantity
+  float4* slice = ln_sm + warp * 3 * Q;
   const Dropout din = make_dropout(p.state, p.p_in, p.site_in);
   const Dropout dout = make_dropout(p.state, p.p_out, p.site_out);
   const __nv_bfloat16* gamma = static_cast<const __nv_bfloat16*>(p.gamma);
-  const float mean = p.mean[row], rstd = p.rstd[row];
-  float gd[NV][8], xh[NV][8];
-  float s1 = 0.f, s2 = 0.f;
-#pragma unroll
-  for (int i = 0; i < NV; ++i) {
-    const int col = i * 256 + lane * 8;
-    float g[8];
-    load8(static_cast<const __nv_bfloat16*>(p.dy) + int64_t(row) * d + col, gd[i]);
-    load8(static_cast<const __nv_bfloat16*>(p.pre) + int64_t(row) * d + col, xh[i]);
-    load8(gamma + col, g);
-    if (dout.active()) {
-      float m[8];
-      dropout_mask8(dout, (uint64_t(row) * d + col) >> 3, m);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) gd[i][j] *= m[j];
-    }
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      xh[i][j] = (xh[i][j] - mean) * rstd;
-      gd[i][j] *= g[j];
-      s1 += gd[i][j];
-      s2 += gd[i][j] * xh[i][j];
-    }
-  }
-  s1 = warp_sum(s1) / float(d);
-  s2 = warp_sum(s2) / float(d);
-#pragma unroll
-  for (int i = 0; i < NV; ++i) {
-    const int col = i * 256 + lane * 8;
-    float dp[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) dp[j] = rstd * (gd[i][j] - s1 - xh[i][j] * s2);
-    store8(static_cast<__nv_bfloat16*>(p.dpre) + int64_t(row) * d + col, dp);
-    if (p.da != nullptr) {
-      if (din.active()) {
-        float m[8];
-        dropout_mask8(din, (uint64_t(row) * d + col) >> 3, m);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) dp[j] *= m[j];
-      }
-      store8(static_cast<__nv_bfloat16*>(p.da) + int64_t(row) * d + col, dp);
-    }
-  }
-}
 
-// partials layout: [gridDim.y][3][d] floats (dgamma, dbeta, dbias); grid (d/256, LN_COL_ROWGROUPS)
-constexpr int LN_COL_ROWGROUPS = 96;  // 3 x 96 = 288 blocks at d = 768: two per SM
-__global__ void __launch_bounds__(256) ln_bwd_cols_kernel(const hstd_ln_bwd_args p) {
-  HSTD_PDL_PROLOGUE();
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int d = p.d;
-  const int col = blockIdx.x * 256 + lane * 8;
-  const Dropout dout = make_dropout(p.state, p.p_out, p.site_out);
-  const __nv_bfloat16* src_a = static_cast<const __nv_bfloat16*>(p.da ? p.da : p.dpre);
-  float ag[8], ab[8], aa[8];
-#pragma unroll
-  for (int j = 0; j < 8; ++j) ag[j] = ab[j] = aa[j] = 0.f;
-  for (int row = blockIdx.y * 8 + warp; row < p.M; row += gridDim.y * 8) {
+#pragma unroll 1
+  for (int r = 0; r < LN_BWD_ROWS; ++r) {
+    const int row = (blockIdx.x * LN_BWD_ROWS + r) * WARPS + warp;
+    if (row >= p.M) {
+      if (r == 0) {
+        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int q = lane; q < 3 * Q; q += 32) slice[q] = z;
+      }
+      continue;
+    }
     const float mean = p.mean[row], rstd = p.rstd[row];
-    float dy[8], x[8], a[8];
-    load8(static_cast<const __nv_bfloat16*>(p.dy) + int64_t(row) * d + col, dy);
-    load8(static_cast<const __nv_bfloat16*>(p.pre) + int64_t(row) * d + col, x);
-    load8(src_a + int64_t(row) * d + col, a);
-    if (dout.active()) {
-      float m[8];
-      dropout_mask8(dout, (uint64_t(row) * d + col) >> 3, m);
+    float gd[NV][8], xh[NV][8];
+    float s1 = 0.f, s2 = 0.f;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) dy[j] *= m[j];
+    for (int i = 0; i < NV; ++i) {
+      const int col = i * 256 + lane * 8;
+      float g[8];
+      load8(static_cast<const __nv_bfloat16*>(p.dy) + int64_t(row) * d + col, gd[i]);
+      load8(static_cast<const __nv_bfloat16*>(p.pre) + int64_t(row) * d + col, xh[i]);
+      load8(gamma + col, g);
+      if (dout.active()) {
+        float m[8];
+        dropout_mask8(dout, (uint64_t(row) * d + col) >> 3, m);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) gd[i][j] *= m[j];
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) xh[i][j] = (xh[i][j] - mean) * rstd;
+      // column contributions of this row: dgamma += dy * xhat, dbeta += dy
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int q = (i * 2 + h) * 32 + lane;
+        float4 cg = make_float4(gd[i][4 * h] * xh[i][4 * h], gd[i][4 * h + 1] * xh[i][4 * h + 1],
+                                gd[i][4 * h + 2] * xh[i][4 * h + 2], gd[i][4 * h + 3] * xh[i][4 * h + 3]);
+        float4 cb = make_float4(gd[i][4 * h], gd[i][4 * h + 1], gd[i][4 * h + 2], gd[i][4 * h + 3]);
+        if (r > 0) {
+          const float4 og = slice[q], ob = slice[Q + q];
+          cg.x += og.x; cg.y += og.y; cg.z += og.z; cg.w += og.w;
+          cb.x += ob.x; cb.y += ob.y; cb.z += ob.z; cb.w += ob.w;
+        }
+        slice[q] = cg;
+        slice[Q + q] = cb;
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        gd[i][j] *= g[j];
+        s1 += gd[i][j];
+        s2 += gd[i][j] * xh[i][j];
+      }
     }
+    s1 = warp_sum(s1) / float(d);
+    s2 = warp_sum(s2) / float(d);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      ag[j] += dy[j] * (x[j] - mean) * rstd;
-      ab[j] += dy[j];
-      aa[j] += a[j];
+    for (int i = 0; i < NV; ++i) {
+      const int col = i * 256 + lane * 8;
+      float dp[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) dp[j] = rstd * (gd[i][j] - s1 - xh[i][j] * s2);
+      store8(static_cast<__nv_bfloat16*>(p.dpre) + int64_t(row) * d + col, dp);
+      if (p.da != nullptr) {
+        if (din.active()) {
+          float m[8];
+          dropout_mask8(din, (uint64_t(row) * d + col) >> 3, m);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) dp[j] *= m[j];
+        }
+        store8(static_cast<__nv_bfloat16*>(p.da) + int64_t(row) * d + col, dp);
+      }
+      // dbias += what the preceding Linear's output gradient is (the value just stored, bf16-rounded)
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int q = (i * 2 + h) * 32 + lane;
+        float4 ca = make_float4(bf16_round(dp[4 * h]), bf16_round(dp[4 * h + 1]), bf16_round(dp[4 * h + 2]),
+                                bf16_round(dp[4 * h + 3]));
+        if (r > 0) {
+          const float4 oa = slice[2 * Q + q];
+          ca.x += oa.x; ca.y += oa.y; ca.z += oa.z; ca.w += oa.w;
+        }
+        slice[2 * Q + q] = ca;
+      }
     }
-  }
-  __shared__ float red[3][8][256];
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    red[0][warp][lane * 8 + j] = ag[j];
-    red[1][warp][lane * 8 + j] = ab[j];
-    red[2][warp][lane * 8 + j] = aa[j];
   }
   __syncthreads();
-  const int c = threadIdx.x;
-  float* out = p.partials + int64_t(blockIdx.y) * 3 * d + blockIdx.x * 256 + c;
+  // fold the warps' slices; position q of quantity k -> columns (q/64)*256 + (q%32)*8 + ((q/32)&1)*4 .. +3
+  float* acc = p.partials;
+  for (int t = threadIdx.x; t < 3 * Q; t += WARPS * 32) {
+    float4 s = ln_sm[t];
 #pragma unroll
-  for (int q = 0; q < 3; ++q) {
-    float s = 0.f;
-#pragma unroll
-    for (int w = 0; w < 8; ++w) s += red[q][w][c];
-    out[q * d] = s;
+    for (int w = 1; w < WARPS; ++w) {
+      const float4 o = ln_sm[w * 3 * Q + t];
+      s.x += o.x; s.y += o.y; s.z += o.z; s.w += o.w;
+    }
+    const int k = t / Q, q = t - k * Q;
+    const int col = (q >> 6) * 256 + (q & 31) * 8 + ((q >> 5) & 1) * 4;
+    red_add_v4(acc + k * 1024 + col, s);
   }
+  __threadfence();
+  __syncthreads();
+  __shared__ int s_last;
+  unsigned int* counter = reinterpret_cast<unsigned int*>(acc + LN_BWD_ACC_FLOATS);
+  if (threadIdx.x == 0) s_last = (atomicAdd(counter, 1u) == gridDim.x - 1) ? 1 : 0;
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  // every block's sums have landed: bf16 gradients out, accumulator back to zero for the next call
+  __nv_bfloat16* outs[3] = {static_cast<__nv_bfloat16*>(p.dgamma), static_cast<__nv_bfloat16*>(p.dbeta),
+                            static_cast<__nv_bfloat16*>(p.dbias)};
+  for (int t = threadIdx.x; t < 3 * d; t += WARPS * 32) {
+    const int k = t / d, c = t - k * d;
+    const float v = __ldcg(acc + k * 1024 + c);
+    if (outs[k]) outs[k][c] = __float2bfloat16_rn(v);
+    __stcg(acc + k * 1024 + c, 0.f);
+  }
+  if (threadIdx.x == 0) *counter = 0u;
 }
 
 // Sum `nparts` partial rows of `width` floats and scatter segments of `seg` columns to up
@@ -458,22 +494,30 @@ extern "C" HSTD_API int hstd_ln_fwd(const hstd_ln_args* a, void* stream) {
   return check_launch("ln_fwd");
 }
 
-extern "C" HSTD_API int64_t hstd_ln_bwd_partials_floats(int d) { return int64_t(LN_BWD_MAX_BLOCKS) * 3 * d; }
+extern "C" HSTD_API int64_t hstd_ln_bwd_partials_floats(int d) { (void)d; return LN_BWD_ACC_FLOATS + 32; }
 
 extern "C" HSTD_API int hstd_ln_bwd(const hstd_ln_bwd_args* a, void* stream) {
   if (int rc = check_d(a->d, "ln_bwd")) return rc;
   if (!a->partials) return set_error(-1, "ln_bwd: partials scratch is required");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  const int blocks = (a->M + LN_WARPS - 1) / LN_WARPS;
-  HSTD_DISPATCH_NV(a->d / 256, launch_pdl(ln_bwd_rows_kernel<NV>, dim3(blocks), dim3(LN_WARPS * 32), 0, s, *a));
-  if (int rc = check_launch("ln_bwd rows")) return rc;
-  launch_pdl(ln_bwd_cols_kernel, dim3(a->d / 256, LN_COL_ROWGROUPS), dim3(256), 0, s, *a);
-  if (int rc = check_launch("ln_bwd cols")) return rc;
-  const int width = 3 * a->d;
-  launch_pdl(partials_finalize_kernel, dim3((width + FIN_COLS - 1) / FIN_COLS), dim3(FIN_COLS * FIN_GROUPS), 0, s,
-             static_cast<const float*>(a->partials), LN_COL_ROWGROUPS, width, a->d, static_cast<__nv_bfloat16*>(a->dgamma),
-             static_cast<__nv_bfloat16*>(a->dbeta), static_cast<__nv_bfloat16*>(a->dbias));
-  return check_launch("ln_bwd finalize");
+  // 16 warps x 2 rows per block: 128 blocks for 4096 tokens, one wave, few block sums to reduce (measured 12.6 us
+  // at d = 768 with dropout against 15.3 us for 8-warp blocks; HSTD_LNB_WARPS=8 selects those)
+  static const int warps = [] { const char* e = getenv("HSTD_LNB_WARPS"); return e && atoi(e) == 8 ? 8 : 16; }();
+  const int rows_per_block = warps * LN_BWD_ROWS;
+  const int blocks = (a->M + rows_per_block - 1) / rows_per_block;
+  const size_t smem = size_t(warps) * 3 * (a->d / 4) * sizeof(float4);
+#define HSTD_LNB_LAUNCH(W_)                                                                                   \
+  HSTD_DISPATCH_NV(a->d / 256, {                                                                               \
+    static bool configured = false;                                                                            \
+    if (!configured) {                                                                                         \
+      cudaFuncSetAttribute(ln_bwd_fused_kernel<NV, W_>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)); \
+      configured = true;                                                                                       \
+    }                                                                                                          \
+    launch_pdl(ln_bwd_fused_kernel<NV, W_>, dim3(blocks), dim3(W_ * 32), smem, s, *a);                        \
+  })
+  if (warps == 16) { HSTD_LNB_LAUNCH(16); } else { HSTD_LNB_LAUNCH(8); }
+#undef HSTD_LNB_LAUNCH
+  return check_launch("ln_bwd");
 }
 
 extern "C" HSTD_API int64_t hstd_colsum_partials_floats(int N) { return int64_t(COLSUM_ROWGROUPS_WS) * N; }

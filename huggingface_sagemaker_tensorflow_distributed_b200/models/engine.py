@@ -394,8 +394,6 @@ class EngineBackend:
                                                     "softmax_bwd", "attn_fwd", "attn_bwd", "head_fwd", "head_bwd",
                                                     "embed_bwd", "colsum", "zero_")), "op")
             plan.names.append(name)
-            if name == "ln_bwd":
-                plan.launches += 1  # rows + cols + finalize
 
         if train:
             o = self.opt
@@ -469,7 +467,9 @@ class EngineBackend:
         dP = None if fused else self._buf(plan, "dP", (B, H, S, S))
         attn_ws = self._shared("attn_ws", K.attn_bwd_workspace_bytes(B, H, S), torch.uint8) if fused else None
         dqkv = self._buf(plan, "dqkv", (M, 3 * d))
-        lnp = self._shared("ln_partials", K.ln_bwd_partials_floats(d))
+        lnp = self._scratch.get("ln_acc")  # fp32 column accumulator of the LayerNorm backward: zero once, kept zeroed
+        if lnp is None:
+            lnp = self._scratch["ln_acc"] = torch.zeros(K.ln_bwd_partials_floats(d), device=self.device)
         self.dp.begin_backward(plan)
         for i in reversed(range(L)):
             pfx = f"layers.{i}."
@@ -479,7 +479,7 @@ class EngineBackend:
                                              gamma=self.W(f"layers.{i}.ln2.weight"), dpre=bufA, da=da2,
                                              dgamma=self.Gr(f"layers.{i}.ln2.weight"), dbeta=self.Gr(f"layers.{i}.ln2.bias"),
                                              dbias=self.Gr(f"layers.{i}.ffn2.bias"), partials=lnp, state=st, p_in=p_hid,
-                                             site_in=i * 8 + 3), 2)
+                                             site_in=i * 8 + 3), 1)
             dg = da2 if da2 is not None else bufA
             # FFN2: dW2, du = (dg·W2) ∘ gelu'(u)
             self._linear_bwd(plan, dg, f[i], pfx + "ffn2", du, M, epilogue=G.EPI_GELU_BWD, aux=u[i], ldaux=F,
@@ -499,7 +499,7 @@ class EngineBackend:
                                              gamma=self.W(f"layers.{i}.ln1.weight"), dpre=bufA, da=da1,
                                              dgamma=self.Gr(f"layers.{i}.ln1.weight"), dbeta=self.Gr(f"layers.{i}.ln1.bias"),
                                              dbias=self.Gr(f"layers.{i}.out.bias"), partials=lnp, state=st,
-                                             p_in=p_attn_out, site_in=i * 8 + 2), 2)
+                                             p_in=p_attn_out, site_in=i * 8 + 2), 1)
             da = da1 if da1 is not None else bufA
             self._linear_bwd(plan, da, ctx[i], pfx + "out", dctx, M, bias_grad=False)
             if fused:
@@ -516,7 +516,7 @@ class EngineBackend:
         # embeddings
         op(lambda: K.ln_bwd(dy=dx, pre=pre0, mean=mean0, rstd=rstd0, gamma=self.W("emb.ln.weight"), dpre=bufA,
                             dgamma=self.Gr("emb.ln.weight"), dbeta=self.Gr("emb.ln.bias"), partials=lnp, state=st,
-                            p_out=p_hid, site_out=9000), 2)
+                            p_out=p_hid, site_out=9000), 1)
         wg, pg = self.Gr("emb.word.weight"), self.Gr("emb.pos.weight")
         if self.dp.sparse_embedding():
             # only the rows that are live in this step are ever read: the marking kernel cleared them long ago

@@ -135,7 +135,9 @@ int hstd_ln_fwd(const hstd_ln_args* args, void* stream);
 /* backward: given dy, recompute xhat from (pre, mean, rstd):
  *   dpre = LN'(dropout_out'(dy)) ; da = dropout_in'(dpre)  (da may be NULL when p_in == 0)
  *   dgamma, dbeta, dbias (= column sums of da, or of dpre when da==NULL) reduced over rows.
- * `partials` is caller scratch of hstd_ln_bwd_partials_floats(d) floats. */
+ * One kernel; the column sums go through `partials`, an fp32 accumulator of hstd_ln_bwd_partials_floats(d)
+ * floats that must be ZERO before the first call and is left zeroed by every call (calls that share it must
+ * not overlap on the GPU). */
 typedef struct hstd_ln_bwd_args {
   const void* dy; const void* pre; const float* mean; const float* rstd; const void* gamma;
   void* dpre; void* da;

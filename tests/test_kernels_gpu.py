@@ -43,7 +43,7 @@ def test_residual_layernorm_fwd_bwd(d):
     F.layer_norm(pre_ref, (d,), gw, gb, 1e-12).backward(dy.float())
     dpre = torch.empty_like(a)
     dgamma, dbeta, dbias = (torch.empty(d, dtype=torch.bfloat16, device="cuda") for _ in range(3))
-    partials = torch.empty(k.ln_bwd_partials_floats(d), device="cuda")
+    partials = torch.zeros(k.ln_bwd_partials_floats(d), device="cuda")  # accumulator: zero once, left zeroed
     k.ln_bwd(dy=dy, pre=pre, mean=mean, rstd=rstd, gamma=gamma, dpre=dpre, dgamma=dgamma, dbeta=dbeta, dbias=dbias,
              partials=partials)
     close(dpre, pre_ref.grad, 3e-2, 3e-2)
@@ -70,7 +70,7 @@ def test_layernorm_dropout_is_replayed_in_backward():
     dy = bf(M, d)
     dpre, da = torch.empty_like(a), torch.empty_like(a)
     dg, db, dbias = (torch.empty(d, dtype=torch.bfloat16, device="cuda") for _ in range(3))
-    partials = torch.empty(k.ln_bwd_partials_floats(d), device="cuda")
+    partials = torch.zeros(k.ln_bwd_partials_floats(d), device="cuda")  # accumulator: zero once, left zeroed
     k.ln_bwd(dy=dy, pre=pre, mean=mean, rstd=rstd, gamma=gamma, dpre=dpre, da=da, dgamma=dg, dbeta=db, dbias=dbias,
              partials=partials, state=st, p_in=p, site_in=7)
     assert torch.equal(da != 0, keep & (dpre != 0))  # same mask as forward

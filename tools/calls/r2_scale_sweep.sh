@@ -31,11 +31,10 @@ print('$label', d.get('ms_per_step'), 'ms', d.get('value'), 'samples/s exposed',
 }
 S="--steps 100 --warmup 8 --exposed_comm"
 run "mb32" HSTD_X=1 -- $S --bucket_mb 32 --timeline gpurun_out/${TAG}_timeline_n${N}.txt
-run "mb16" HSTD_X=1 -- $S --bucket_mb 16
-run "mb64" HSTD_X=1 -- $S --bucket_mb 64
 run "mb32-two_shot" HSTD_AR_MODE=two_shot -- $S --bucket_mb 32
-run "mb32-one-launch" HSTD_AR_SPLIT=0 -- $S --bucket_mb 32
+run "mb32-nvls" HSTD_AR_MODE=nvls -- $S --bucket_mb 32
+run "mb16" HSTD_X=1 -- $S --bucket_mb 16
 if [ "${MORE:-0}" = "1" ]; then
+  run "mb32-one-launch" HSTD_AR_SPLIT=0 -- $S --bucket_mb 32
   run "mb32-dense-emb" HSTD_SPARSE_EMB=0 -- $S --bucket_mb 32
-  run "mb32-blocks64" HSTD_AR_BLOCKS=64 -- $S --bucket_mb 32
 fi
