@@ -17,7 +17,20 @@ def build(cfg, device, world: int, lr: float, sdpa: bool = True, capturable: boo
 
     torch.manual_seed(42)
     model = EncoderForSequenceClassification(cfg, sdpa=sdpa).to(device)
-    if world > 1:
+    if world > 1 and capturable:
+        # CUDA-graph arm: DistributedDataParallel's reducer does not survive stream capture here
+        # (cudaErrorStreamCaptureImplicit), plain NCCL collectives do.  Gradients are views into ONE flat buffer
+        # that is all-reduced with NCCL after backward (no overlap with backward: noted in the bench line).
+        params = [p for p in model.parameters()]
+        flat = torch.zeros(sum(p.numel() for p in params), device=device)
+        off = 0
+        for p in params:
+            p.grad = flat[off:off + p.numel()].view_as(p)
+            off += p.numel()
+        model._flat_grad, model._world = flat, world
+        for p in params:  # rank 0's initial weights everywhere, as DDP's constructor does
+            dist.broadcast(p.data, src=0)
+    elif world > 1:
         model = torch.nn.parallel.DistributedDataParallel(model, device_ids=[device.index], bucket_cap_mb=25,
                                                           gradient_as_bucket_view=True)
     opt = torch.optim.AdamW(model.parameters(), lr=lr, eps=1e-7, weight_decay=0.0, fused=True, capturable=capturable)
@@ -25,11 +38,18 @@ def build(cfg, device, world: int, lr: float, sdpa: bool = True, capturable: boo
 
 
 def train_step(model, opt, ids, mask, labels):
-    opt.zero_grad(set_to_none=True)
+    flat = getattr(model, "_flat_grad", None)
+    if flat is None:
+        opt.zero_grad(set_to_none=True)
+    else:
+        flat.zero_()
     with torch.autocast("cuda", dtype=torch.bfloat16):
         logits = model(ids, mask)
     loss = F.cross_entropy(logits.float(), labels)
     loss.backward()
+    if flat is not None:
+        dist.all_reduce(flat)
+        flat.mul_(1.0 / model._world)
     opt.step()
     return loss
 
@@ -52,8 +72,11 @@ class GraphedStep:
         cur.wait_stream(side)
         torch.cuda.synchronize()
         self.graph = torch.cuda.CUDAGraph()
-        opt.zero_grad(set_to_none=True)
-        with torch.cuda.graph(self.graph):
+        if getattr(model, "_flat_grad", None) is None:
+            opt.zero_grad(set_to_none=True)
+        # thread_local: the NCCL watchdog thread polls events while we capture; the default (global) mode
+        # treats that as an illegal call during capture (cudaErrorStreamCaptureImplicit)
+        with torch.cuda.graph(self.graph, capture_error_mode="thread_local"):
             self.loss = train_step(model, opt, self.ids, self.mask, self.labels)
         torch.cuda.synchronize()
 

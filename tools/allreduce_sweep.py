@@ -31,11 +31,38 @@ def timed(fn, iters, dev):
     return t.item() * 1e3  # us
 
 
+def check_values(grp, numel, mode, name, W, R, dev):
+    """One averaging all-reduce of rank-dependent data against the gathered fp32 mean, and bit-equality of the
+    result on every rank (the timing loops below say nothing about correctness)."""
+    g = torch.Generator(device=dev).manual_seed(1234 + R)
+    grp.g16[:numel].copy_((torch.randn(numel, device=dev, generator=g) * (1 + R)).bfloat16())
+    grp.w16[:numel].zero_()
+    torch.cuda.synchronize()
+    dist.barrier()
+    parts = [torch.empty(numel, dtype=torch.bfloat16, device=dev) for _ in range(W)]
+    dist.all_gather(parts, grp.g16[:numel].contiguous())
+    want = torch.stack([p.float() for p in parts]).sum(0) / W
+    del parts
+    dist.barrier()
+    grp.launch(grp.make_args(0, 0, numel, mode, update=False, blocks=64))
+    torch.cuda.synchronize()
+    dist.barrier()
+    got = (grp.w16 if mode == p2p.AR_ONE_SHOT else grp.g16)[:numel]
+    err = (got.float() - want).abs().max().item()
+    assert err <= 2 ** -7 * want.abs().max().item() + 1e-6, (name, numel, err)
+    outs = [torch.empty_like(got) for _ in range(W)]
+    dist.all_gather(outs, got.contiguous())
+    assert all(torch.equal(outs[0], o) for o in outs), f"{name}: ranks hold different results at {numel} elements"
+    grp.check_errors()
+    grp.g16[:numel].normal_()
+
+
 def main():
     hvd.init()
     W, R, dev = hvd.size(), hvd.rank(), comm.device()
     max_bytes = int(os.environ.get("SWEEP_MAX_BYTES", str(1 << 30)))
     sizes = [1 << k for k in range(10, 31) if (1 << k) <= max_bytes]
+    check_max_bytes = int(os.environ.get("SWEEP_CHECK_MAX_BYTES", str(16 << 20)))
     total = max_bytes // 2
     grp = p2p.P2PGroup(total, [Bucket(0, 0, total, [])], dev)
     grp.g16.normal_()
@@ -53,14 +80,17 @@ def main():
         for name, mode in modes:
             if mode == p2p.AR_ONE_SHOT and nbytes > (64 << 20):
                 continue
+            if nbytes <= check_max_bytes:
+                check_values(grp, numel, mode, name, W, R, dev)
+                row["values_checked"] = True
             best = None
-            for blocks in (8, 32, 64, 128):
-                if blocks * 512 * 8 > numel * 4 and blocks > 8:
+            for blocks, tail in ((8, False), (32, False), (128, False), (32, True), (128, True)):
+                if blocks * 128 * (4 if tail else 1) * 8 > numel * 4 and blocks > 8:
                     continue
-                args = grp.make_args(0, 0, numel, mode, update=False, blocks=blocks)
+                args = grp.make_args(0, 0, numel, mode, update=False, blocks=blocks, tail=tail)
                 us = timed(lambda: grp.launch(args), iters, dev)
                 if best is None or us < best[0]:
-                    best = (us, blocks)
+                    best = (us, f"{blocks}x{512 if tail else 128}")
             row[name + "_us"], row[name + "_blocks"] = best
         grp.check_errors()
         rows.append(row)
@@ -70,7 +100,7 @@ def main():
             for name, _ in modes:
                 if name + "_us" in row:
                     us = row[name + "_us"]
-                    msg += f" | {name} {us:9.1f} us {row['bytes']*f/us/1e3:7.1f} GB/s (b{row[name+'_blocks']})"
+                    msg += f" | {name} {us:9.1f} us {row['bytes']*f/us/1e3:7.1f} GB/s ({row[name+'_blocks']})"
             print(msg, flush=True)
     if R == 0:
         os.makedirs("gpurun_out", exist_ok=True)

@@ -85,8 +85,17 @@ def run(model_name="distilbert-base-uncased", steps=300, batch=8, seq=512, dropo
     so, st_ = smooth(lo), smooth(lt)
     d_raw = [abs(a - b) for a, b in zip(lo, lt)]
     d_sm = [abs(a - b) for a, b in zip(so, st_)]
+    d_w50 = [abs(a - b) for a, b in zip(smooth(lo, 50), smooth(lt, 50))]
+
+    def crossing(x, thr):  # first step whose 10-step mean is below thr
+        return next((i + 1 for i, v in enumerate(smooth(x)) if i >= 9 and v < thr), None)
+
     res = {"model": model_name, "n_gpus": world, "steps": steps, "per_gpu_batch": batch, "seq_len": seq, "dropout": dropout,
            "max_abs_diff": max(d_raw), "mean_abs_diff": sum(d_raw) / len(d_raw), "max_abs_diff_smoothed": max(d_sm),
+           # bf16 training is chaotic once the loss starts to collapse: identical for the first tens of steps, then the
+           # two arms spike at different steps while following the same envelope (50-step means, threshold crossings)
+           "max_abs_diff_first50": max(d_raw[:50]), "max_abs_diff_window50": max(d_w50[49:]) if steps >= 50 else None,
+           "steps_to_loss_below": {str(t): [crossing(lo, t), crossing(lt, t)] for t in (0.5, 0.3, 0.1)},
            "first_loss": [lo[0], lt[0]], "last10_mean": [sum(lo[-10:]) / 10, sum(lt[-10:]) / 10]}
     if rank == 0:
         log(json.dumps(res))
