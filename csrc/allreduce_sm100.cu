@@ -563,7 +563,10 @@ static int check_rows(const hstd_allreduce_args* a) {
   if (!a->update) return set_error(-1, "allreduce: row filters exist for the fused optimizer form only");
   if (!a->row_stamp || a->row_elems <= 0 || a->row_elems % 8 != 0)
     return set_error(-1, "allreduce: row filter needs row_stamp and row_elems (multiple of 8)");
-  if (a->numel % a->row_elems != 0) return set_error(-1, "allreduce: a row-sparse bucket must be whole rows");
+  // (a rank on its own — world 1, the exposed-communication timing aid — works on its slice of the bucket, which
+  // need not start or end on a row boundary: rows are looked up per vector through row_elem0)
+  if (a->world > 1 && a->numel % a->row_elems != 0)
+    return set_error(-1, "allreduce: a row-sparse bucket must be whole rows");
   if (a->mode == HSTD_AR_ONE_SHOT) return set_error(-1, "allreduce: row filters need the sharded (two-shot / NVLS) form");
   return 0;
 }

@@ -263,10 +263,11 @@ def check_training():
             # Elements whose gradient is rounding noise move by +-lr per step under Adam in either run, so the
             # max-abs difference can approach the total movement (32 steps x 2e-4); the bulk must agree closely.
             diff = flat - p2p_flat
-            assert diff.abs().max().item() < 1.3e-2, diff.abs().max().item()
-            assert (diff.norm() / flat.norm()).item() < 2e-2, (diff.norm() / flat.norm()).item()
+            travel = 32 * 1e-4 * W  # steps x learning rate (lr scales with the world size, scripts/train.py:112)
+            assert diff.abs().max().item() < 2.1 * travel, diff.abs().max().item()
+            assert (diff.norm() / flat.norm()).item() < 1e-2 * W, (diff.norm() / flat.norm()).item()
     lp, ln = losses["p2p"], losses["nccl"]
-    assert abs(lp[-1] - ln[-1]) < 2e-2, losses
+    assert abs(lp[-1] - ln[-1]) < 1e-2 * W, losses
     log("OK training p2p==nccl", lp, ln)
 
 

@@ -26,13 +26,32 @@ print('$label', d.get('ms_per_step'), 'ms', d.get('value'), 'samples/s  e2e', d.
 if [ "$N" != "1" ] && [ "${SKIP_TESTS:-0}" != "1" ]; then
   timeout 500 python -m pytest tests/test_multigpu.py -q -k "${N}]" > $OUT/tests.log 2>&1; echo "tests rc=$?" >> $OUT/tests.log; tail -4 $OUT/tests.log
 fi
+if [ "${VARIANTS:-0}" = "1" ] && [ "$N" != "1" ]; then
+  # schedule x reduction variant at this world size; the fastest becomes the setting for the rest of the call
+  for sp in 1 0; do for md in nvls two_shot; do
+    HSTD_AR_SPLIT=$sp HSTD_AR_MODE=$md bench "variant-split${sp}-${md}" --steps 100 --warmup 8 --exposed_comm
+  done; done
+  eval $(python - $J <<'PY'
+import json, sys
+best = None
+for l in open(sys.argv[1]):
+    d = json.loads(l)
+    if d.get("label", "").startswith("variant-") and (best is None or d["ms_per_step"] < best["ms_per_step"]):
+        best = d
+if best:
+    _, sp, md = best["label"].split("-")
+    print(f"export HSTD_AR_SPLIT={sp[-1]} HSTD_AR_MODE={md}")
+PY
+)
+  echo "chosen: HSTD_AR_SPLIT=${HSTD_AR_SPLIT:-} HSTD_AR_MODE=${HSTD_AR_MODE:-}" | tee $OUT/chosen_variant.txt
+fi
 bench distilbert --steps 200 --warmup 8 --exposed_comm
 bench bert-base --model bert-base-uncased --steps 100 --warmup 6 --exposed_comm
 if [ "${LARGE:-0}" = "1" ]; then
   bench bert-large --model bert-large-uncased --steps 40 --warmup 4
   bench roberta-large --model roberta-large --steps 40 --warmup 4
 fi
-bench distilbert-ddp-graph --impl ddp --graph --steps 100 --warmup 5
+BENCH_TIMEOUT=100 bench distilbert-ddp-graph --impl ddp --graph --steps 100 --warmup 5
 if [ "${DDP_MORE:-0}" = "1" ]; then
   bench distilbert-ddp-eager --impl ddp --steps 60 --warmup 5
   bench bert-base-ddp-graph --impl ddp --graph --model bert-base-uncased --steps 60 --warmup 5
@@ -43,7 +62,9 @@ if [ "$N" != "1" ]; then
   tail -4 $OUT/allreduce_sweep.txt
 fi
 timeout 300 $(tr) tools/loss_parity.py --model distilbert-base-uncased --steps ${PARITY_STEPS:-300} --dropout 0 --out $OUT/loss_parity.jsonl 2> $OUT/err_parity.log | tail -1
-timeout 300 $(tr) tools/loss_parity.py --model distilbert-base-uncased --steps ${PARITY_STEPS:-300} --dropout 0.1 --out $OUT/loss_parity.jsonl 2>> $OUT/err_parity.log | tail -1
+if [ "${PARITY_DROPOUT:-1}" = "1" ]; then
+  timeout 300 $(tr) tools/loss_parity.py --model distilbert-base-uncased --steps ${PARITY_STEPS:-300} --dropout 0.1 --out $OUT/loss_parity.jsonl 2>> $OUT/err_parity.log | tail -1
+fi
 if [ "${LARGE:-0}" = "1" ]; then
   timeout 300 $(tr) tools/loss_parity.py --model bert-large-uncased --steps 100 --dropout 0 --out $OUT/loss_parity.jsonl 2>> $OUT/err_parity.log | tail -1
 fi

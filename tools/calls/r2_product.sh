@@ -30,7 +30,9 @@ PY
   tail -1 $OUT/${tag}_n${N}/reload.txt
 }
 job distilbert_sharded distilbert-base-uncased '{"eval_batch_size": 64, "log_every": 100}'
+if [ "${NO_SHARD:-1}" = "1" ]; then
 job distilbert_no_shard distilbert-base-uncased '{"no_shard": true, "eval_batch_size": 64, "max_eval_steps": 50, "log_every": 500}'
+fi
 job bertlarge_sharded bert-large-uncased-whole-word-masking '{"eval_batch_size": 64, "log_every": 100}'
 job distilbert_single_node distilbert-base-uncased "{\"train_batch_size\": $((8*N)), \"eval_batch_size\": 64, \"max_eval_steps\": 50, \"log_every\": 100}" singe_node_train.py
 cat $OUT/jobs_n${N}.jsonl
