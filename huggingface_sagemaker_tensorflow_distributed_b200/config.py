@@ -73,7 +73,8 @@ class TrainConfig:
     log_every: int = 50
     metrics_jsonl: Optional[str] = None
     save_training_state: bool = False  # also write optimizer moments + step (true resume)
-    data_source: str = "ids"  # ids: synthetic token ids | text: synthetic reviews through the native tokenizer
+    # ids: synthetic token ids | text: synthetic reviews through the native tokenizer | hf:<name or dir>: load_dataset route
+    data_source: str = "ids"
     prefetch: bool = True  # C++ batch loader thread + pinned ring (GPU runs)
     train_channel: Optional[str] = None  # SM_CHANNEL_TRAIN
     test_channel: Optional[str] = None  # SM_CHANNEL_TEST
@@ -118,7 +119,8 @@ def build_parser(distributed: bool = True) -> argparse.ArgumentParser:
     p.add_argument("--log_every", type=int, default=50)
     p.add_argument("--metrics_jsonl", type=str, default=None)
     p.add_argument("--save_training_state", type=str2bool, nargs="?", const=True, default=False)
-    p.add_argument("--data_source", type=str, default="ids", choices=["ids", "text"])
+    p.add_argument("--data_source", type=str, default="ids",
+                   help="ids | text | hf:<dataset name in the local HF cache or save_to_disk directory> (e.g. hf:imdb)")
     p.add_argument("--prefetch", type=str2bool, nargs="?", const=True, default=True)
     p.add_argument("--train_channel", type=str, default=env.get("SM_CHANNEL_TRAIN"))
     p.add_argument("--test_channel", type=str, default=env.get("SM_CHANNEL_TEST"))

@@ -11,6 +11,8 @@ sequence length, feeding only ``input_ids`` and ``attention_mask``.  A small pla
 ``.jsonl`` text plus a loadable tokenizer, those are used instead.  ``data_source="text"``
 generates synthetic review *texts* and runs them through the native C++ WordPiece tokenizer
 (csrc/tokenizer.cpp) — the reference's ``dataset.map(tokenize, batched=True)`` stage.
+``data_source="hf:imdb"`` (or ``hf:<save_to_disk dir>``) is the reference's own ``load_dataset`` route, for
+machines that have the dataset in their HF cache.
 
 Batching: ``BatchedDataset`` assembles batches in Python; with ``prefetch=True`` a C++ worker
 thread (csrc/batch_loader.cpp) stages them ahead of the training loop into a ring of pinned
@@ -142,6 +144,43 @@ def load_channel(path: str, cfg: EncoderConfig, seq_len: int, tokenizer=None) ->
     return None
 
 
+def load_hf_text_dataset(cfg: EncoderConfig, tokenizer, seq_len: int, name_or_dir: str = "imdb",
+                         max_train: int = -1, max_test: int = -1) -> Optional[Tuple[TokenizedDataset, TokenizedDataset]]:
+    """The reference's real-data path (scripts/train.py:69-100): ``load_dataset("imdb", split=["train","test"])``
+    -> ``tokenizer(text, truncation=True, padding=...)`` -> dense ``[N, model_max_length]`` ids / mask + label.
+    ``name_or_dir`` is a hub dataset name served from the local HF cache (there is no network here:
+    ``HF_DATASETS_OFFLINE``) or a directory written by ``DatasetDict.save_to_disk``.  Returns None when the
+    ``datasets`` library, the data or a tokenizer is not available, so callers fall back to synthetic data."""
+    if tokenizer is None:
+        return None
+    try:
+        import datasets as hfds
+
+        if os.path.isdir(name_or_dir):
+            dd = hfds.load_from_disk(name_or_dir)
+            train, test = dd["train"], dd["test"]
+        else:
+            train, test = hfds.load_dataset(name_or_dir, split=["train", "test"])
+    except Exception:  # noqa: BLE001 - not cached / offline / library missing
+        return None
+    out = []
+    for split, padding, cap in ((train, "longest", max_train), (test, "max_length", max_test)):
+        if cap is not None and cap >= 0:
+            split = split.select(range(min(cap, len(split))))
+        texts, labels = list(split["text"]), np.asarray(split["label"], dtype=np.int32)
+        if hasattr(tokenizer, "encode_dense"):  # the native tokenizers
+            ids, mask = tokenizer.encode_dense(texts, max_length=seq_len, padding=padding)
+        else:
+            enc = tokenizer(texts, truncation=True, padding=padding, max_length=seq_len)
+            ids, mask = np.asarray(enc["input_ids"], dtype=np.int32), np.asarray(enc["attention_mask"], dtype=np.int32)
+        ids, mask = _pad_to(np.asarray(ids, dtype=np.int32), seq_len, 0), _pad_to(np.asarray(mask, dtype=np.int32), seq_len, 0)
+        ids = np.where(mask == 1, ids, cfg.pad_token_id).astype(np.int32)
+        if int(ids.max()) >= cfg.vocab_size:
+            raise ValueError(f"tokenizer produced id {int(ids.max())} >= model vocab_size {cfg.vocab_size}")
+        out.append(TokenizedDataset(np.ascontiguousarray(ids), np.ascontiguousarray(mask), labels, source=f"hf:{name_or_dir}"))
+    return out[0], out[1]
+
+
 def try_load_tokenizer(name_or_path: Optional[str]):
     """``AutoTokenizer.from_pretrained`` (scripts/train.py:69): the tokenizer files of a local
     directory when present, otherwise a synthetic WordPiece vocabulary of the model's size served
@@ -271,6 +310,13 @@ def build_datasets(cfg: EncoderConfig, *, train_samples: int, test_samples: int,
     test = load_channel(test_channel, cfg, seq_len, tokenizer) if test_channel else None
     if data_source == "text" and tokenizer is None:
         raise ValueError("data_source='text' needs a tokenizer")
+    if data_source.startswith("hf:") and (train is None or test is None):
+        # hf:imdb (local HF cache) or hf:/path/to/save_to_disk dir — the reference's load_dataset route
+        got = load_hf_text_dataset(cfg, tokenizer, seq_len, data_source[3:], train_samples, test_samples)
+        if got is None:
+            raise ValueError(f"data_source={data_source!r}: dataset, `datasets` library or tokenizer unavailable offline")
+        train, test = (train or got[0]), (test or got[1])
+        data_source = "ids"
     if train is None:
         # the reference pads the train split to the longest example and the test split to max_length
         # before densifying both to model_max_length (scripts/train.py:76,90)

@@ -61,3 +61,30 @@ def test_uneven_shards_take_the_same_number_of_steps():
             if r > 0:  # the extra batch of a short rank is all padding
                 assert (batches[-1][1] == IGNORE_LABEL).all()
         assert lens == [2] * 8 and seen == 65
+
+
+def test_hf_datasets_route_like_the_reference(tmp_path):
+    """load_dataset -> tokenizer(truncation, padding) -> dense [N, max_len] tables (scripts/train.py:69-100), from a
+    local DatasetDict (no network here): train split padded to the longest example, test to max_length, both
+    densified to the model's sequence length."""
+    import datasets as hfds
+
+    from huggingface_sagemaker_tensorflow_distributed_b200.data import try_load_tokenizer
+
+    dd = hfds.DatasetDict({
+        "train": hfds.Dataset.from_dict({"text": ["a fine film", "dull and far too long , really", "ok"], "label": [1, 0, 1]}),
+        "test": hfds.Dataset.from_dict({"text": ["not bad at all", "awful"], "label": [1, 0]}),
+    })
+    dd.save_to_disk(str(tmp_path / "imdb_local"))
+    cfg = resolve_config("tiny-bert")
+    tok = try_load_tokenizer("tiny-bert")
+    if tok is None:
+        import pytest
+        pytest.skip("native tokenizer library not built")
+    train, test = build_datasets(cfg, train_samples=-1, test_samples=-1, seq_len=32, seed=0, tokenizer=tok,
+                                 data_source="hf:" + str(tmp_path / "imdb_local"))
+    assert train.input_ids.shape == (3, 32) and test.input_ids.shape == (2, 32)
+    assert list(train.labels) == [1, 0, 1] and list(test.labels) == [1, 0]
+    assert (train.attention_mask.sum(1) >= 3).all() and train.input_ids.max() < cfg.vocab_size
+    assert ((train.attention_mask == 0) <= (train.input_ids == cfg.pad_token_id)).all()
+    assert train.source.startswith("hf:")

@@ -16,7 +16,8 @@ for f in funcs:
     name = f.split("\n", 1)[0].strip()
     c = collections.Counter()
     for mn in ("UTCHMMA", "UTCHMMA.2CTA", "UTCBAR", "LDTM", "UTMALDG", "UTMALDG.4D.2CTA", "UTMASTG", "SYNCS", "HMMA", "MUFU.EX2",
-               "FFMA2", "FADD2", "FMUL2", "LDGMC", "STG.E.128.STRONG.SYS", "LDG.E.128.STRONG.SYS", "ACQBULK", "ELECT"):
+               "FFMA2", "FADD2", "FMUL2", "LDGMC", "STG.E.128.STRONG.SYS", "LDG.E.128.STRONG.SYS", "ACQBULK", "ELECT",
+               "REDG.E.ADD.F32", "MUFU.RCP", "MUFU.SQRT"):
         c[mn] = len(re.findall(r"(?<![A-Z0-9.])" + re.escape(mn), f))
     rows.append((name, c))
 import subprocess
@@ -31,7 +32,8 @@ with open("profiles/sass/summary.txt", "w") as w:
     w.write("SASS mnemonic counts per kernel of libhstd_b200.so (sm_100a).  UTCHMMA = tcgen05.mma (.2CTA = cta_group::2),\n"
             "LDTM = tcgen05.ld, UTMALDG / UTMASTG = TMA tensor load / store, UTCBAR = tcgen05.commit, SYNCS = mbarrier ops,\n"
             "FFMA2 / FADD2 / FMUL2 = packed fp32x2 arithmetic (sm_100), ELECT = elect.sync, ACQBULK = griddepcontrol.wait,\n"
-            "LDGMC = multimem.ld_reduce (in-switch NVLS reduction), *.STRONG.SYS = peer loads/stores over NVLink.\n"
+            "LDGMC = multimem.ld_reduce (in-switch NVLS reduction), *.STRONG.SYS = peer loads/stores over NVLink,\n"
+            "REDG.E.ADD.F32 = red.global.add.v4.f32 (column sums of the fused LayerNorm backward).\n"
             "HMMA (legacy mma.sync) must be 0 everywhere.\n\n")
     for name, c in sorted(rows, key=lambda r: -r[1]["UTCHMMA"]):
         d = dem.get(name, name)
@@ -48,10 +50,12 @@ funcs = re.split(r"\n(?=\s*Function : )", txt)
 want = {"gemm_256x256_2sm_TN": "gemm_bf16_kernelILi256ELb0ELb0ELi2E", "gemm_wgrad_128_1sm": "gemm_bf16_kernelILi128ELb1ELb1ELi1E",
         "gemm_192_1sm_TN": "gemm_bf16_kernelILi192ELb0ELb0ELi1E",
         "attn_fwd_S512": "attn_fwd_kernelILi4E", "attn_bwd_S512": "attn_bwd_kernelILi4E",
-        "fused_allreduce_nvls_adamw_w8": "fused_allreduce_kernelILi8ELi2ELb1E",
-        "fused_allreduce_two_shot_adamw_w8": "fused_allreduce_kernelILi8ELi0ELb1E",
+        "fused_allreduce_nvls_adamw_w8_coresident": "fused_allreduce_kernelILi8ELi2ELb1ELi0ELi128E",
+        "fused_allreduce_nvls_adamw_w8_tail_rows_both": "fused_allreduce_kernelILi8ELi2ELb1ELi3ELi512E",
+        "fused_allreduce_two_shot_adamw_w2_coresident": "fused_allreduce_kernelILi2ELi0ELb1ELi0ELi128E",
+        "sparse_rows_mark": "mark_rows_kernelENS_14ArKernelParamsE",
         "ln_fwd_residual_dropout_d768": "ln_fwd_kernelILi3ELb0E", "ln_fwd_embedding_d768": "ln_fwd_kernelILi3ELb1E",
-        "ln_bwd_rows_d768": "ln_bwd_rows_kernelILi3E", "head_logits_xent": "head_logits_loss_kernel",
+        "ln_bwd_fused_d768": "ln_bwd_fused_kernelILi3ELi16E", "head_logits_xent": "head_logits_loss_kernel",
         "adamw_flat": "adamw_flat_kernel"}
 for out, key in want.items():
     for f in funcs:
