@@ -52,6 +52,20 @@ def test_allreduce_flag_protocol_orders_gradient_reads_and_weight_writes():
     assert broken > 20  # without the end barrier most timings expose a violation
 
 
+def test_split_schedule_protocol_needs_exactly_the_barriers_it_has():
+    """Round-2 schedule (id marking | reduce-only launches with a start barrier under backward | update-only
+    launches at the end, the last one closing the step): two in-order agents per rank, random timings.  No stale id /
+    gradient read, no weight slice overwritten under a rank that still computes with it, no forward on half-updated
+    weights, no deadlock — and the model must notice when the closing barrier is dropped or when weights are
+    written before the last reduce barrier has shown that every rank finished backward."""
+    import protocol_sim as ps
+
+    for world in (2, 4, 8):
+        assert ps.check_allreduce_split(world, runs=40), world
+    assert not ps.check_allreduce_split(4, runs=60, broken="no_final_barrier")
+    assert not ps.check_allreduce_split(4, runs=60, broken="update_before_last_reduce")
+
+
 def test_round2_forward_pingpong_design_is_consistent():
     """Design study kept executable: two query tiles per CTA with single S / P buffers per tile and
     2-deep K / V rings must be deadlock- and hazard-free, and clearly faster per tile than the

@@ -390,6 +390,160 @@ def check_allreduce(world: int, runs: int = 300) -> bool:
 
 
 # ---------------------------------------------------------------------------------------------
+# Round-2 all-reduce schedule: id marking | reduce-only launches under backward | update-only launches at the end
+# ---------------------------------------------------------------------------------------------
+def allreduce_split_protocol(sim: Sim, world: int, steps: int, buckets: int = 3, broken: str = "") -> None:
+    """Two in-order agents per rank, as in the captured graph: MAIN (stage ids, forward, backward bucket by bucket,
+    embedding scatter) and COMM (mark kernel; one reduce-only launch per bucket as its gradients complete; then the
+    update-only launches of all buckets, the last one closing the step with a barrier).  Flag slots: one per bucket
+    plus one for the marking kernel, monotone values, >= comparison.
+      mark(t)    : barrier | read every rank's ids | clear live gradient rows | barrier
+      reduce(k,t): barrier | read every rank's gradients of bucket k | write the average into the OWN slice
+      update(k,t): AdamW | store the new weights of the own slice into every rank's arena ; last k: barrier
+    Invariants: ids and gradients read from a peer belong to the current step; no weight slice is overwritten while
+    its owner... reader is still inside forward / backward of the step that must see the old value; every forward
+    starts with all slices at the previous step's version; no deadlock.
+    `broken`: "no_final_barrier" | "update_before_last_reduce" must each be caught.  ("no_mark_end_barrier" is
+    NOT caught: the model shows the marking kernel's second barrier to be redundant, because no rank can finish
+    a step — and restage its ids — before every peer has passed the later reduce barriers of that step, which
+    its in-order comm stream reaches only after its marking kernel.  The kernel keeps it; it is off the critical
+    path.)"""
+    nslots = buckets + 1
+    flags = [[[0] * world for _ in range(world)] for _ in range(nslots)]  # flags[slot][r][p]
+    epoch = [[0] * nslots for _ in range(world)]
+    ids_ver = [-1] * world
+    grad_ver = [[-1] * buckets for _ in range(world)]
+    weight_ver = [[[-1] * buckets for _ in range(world)] for _ in range(world)]  # [r][s][k]: slice s of bucket k in r's arena
+    in_compute = [None] * world                            # step whose forward/backward rank r is inside, else None
+    local = [dict() for _ in range(world)]                 # rank-local events: name -> True
+    waiting: List[tuple] = []
+
+    def ready(req):
+        if req[0] == "flagwait":
+            _, slot, r, peer, val = req
+            return flags[slot][r][peer] >= val
+        _, r, name = req  # ("local", r, name)
+        return local[r].get(name, False)
+
+    def poll():
+        still = []
+        for (gen, req) in waiting:
+            if ready(req):
+                sim.at(sim.jitter(30), lambda g=gen: step_agent(g))
+            else:
+                still.append((gen, req))
+        waiting[:] = still
+
+    def step_agent(gen):
+        try:
+            req = next(gen)
+        except StopIteration:
+            sim.live -= 1
+            return
+        if req[0] == "delay":
+            sim.at(req[1], lambda: step_agent(gen))
+        elif ready(req):
+            sim.at(sim.jitter(30), lambda: step_agent(gen))
+        else:
+            waiting.append((gen, req))
+
+    def set_local(r, name):
+        local[r][name] = True
+        poll()
+
+    def barrier(r, slot):
+        epoch[r][slot] += 1
+        val = epoch[r][slot]
+        for peer in range(world):
+            def land(p=peer, v=val):
+                flags[slot][p][r] = max(flags[slot][p][r], v)
+                poll()
+            sim.at(sim.jitter(60), land)
+        for peer in range(world):
+            yield ("flagwait", slot, r, peer, val)
+
+
+    def main(r):
+        for t in range(steps):
+            # the host stages step t's ids into the peer-visible slot (stream-ordered behind step t-1's graph,
+            # i.e. behind this rank's comm agent of step t-1)
+            if t > 0:
+                yield ("local", r, f"comm_done{t - 1}")
+            ids_ver[r] = t
+            set_local(r, f"ids{t}")
+            for sl in range(world):
+                for k in range(buckets):
+                    if weight_ver[r][sl][k] != t - 1:
+                        sim.hazards.append(f"rank {r} starts forward {t} with slice {sl} of bucket {k} at version {weight_ver[r][sl][k]}")
+            in_compute[r] = t
+            yield ("delay", sim.jitter(1500, 0.8))          # forward
+            for k in range(buckets):                         # backward, gradients complete bucket by bucket
+                yield ("delay", sim.jitter(500, 0.8))
+                if k == buckets - 1:                         # embedding scatter-add needs the cleared live rows
+                    yield ("local", r, f"marked{t}")
+                grad_ver[r][k] = t
+                if k == buckets - 1:
+                    in_compute[r] = None                     # weights are no longer read by this rank in step t
+                set_local(r, f"grads{t}.{k}")
+
+    def comm(r):
+        for t in range(steps):
+            yield ("local", r, f"ids{t}")
+            yield from barrier(r, buckets)                   # mark: every rank has staged its ids
+            for peer in range(world):
+                yield ("delay", sim.jitter(30))
+                if ids_ver[peer] != t:
+                    sim.hazards.append(f"rank {r} mark {t} reads rank {peer}'s ids of step {ids_ver[peer]}")
+            if broken != "no_mark_end_barrier":
+                yield from barrier(r, buckets)               # peers have read our ids
+            set_local(r, f"marked{t}")
+            for k in range(buckets):
+                if broken == "update_before_last_reduce" and k == buckets - 1:
+                    yield from update(r, t, range(buckets - 1), last=False)
+                yield ("local", r, f"grads{t}.{k}")
+                yield from barrier(r, k)                     # reduce-only launch: start barrier only
+                for peer in range(world):
+                    yield ("delay", sim.jitter(40))
+                    if grad_ver[peer][k] != t:
+                        sim.hazards.append(f"rank {r} reduce({k},{t}) reads rank {peer}'s gradients of step {grad_ver[peer][k]}")
+            todo = range(buckets - 1, buckets) if broken == "update_before_last_reduce" else range(buckets)
+            yield from update(r, t, todo, last=True)
+            set_local(r, f"comm_done{t}")
+
+    def update(r, t, ks, last):
+        ks = list(ks)
+        for i, k in enumerate(ks):
+            yield ("delay", sim.jitter(150))                 # AdamW on the owned slice of bucket k
+            for peer in range(world):
+                def land(p=peer, tt=t, kk=k):
+                    if in_compute[p] is not None and in_compute[p] <= tt:
+                        sim.hazards.append(f"rank {r} overwrites weights of rank {p} (step {tt}) while it computes step {in_compute[p]}")
+                    weight_ver[p][r][kk] = tt
+                sim.at(sim.jitter(60), land)
+            yield ("delay", 80)                              # system-scope fence before the closing release
+            if last and i == len(ks) - 1 and broken != "no_final_barrier":
+                yield from barrier(r, k)                     # closing barrier of the step
+
+    for r in range(world):
+        sim.live += 2
+        step_agent(main(r))
+        step_agent(comm(r))
+
+
+def check_allreduce_split(world: int, runs: int = 200, broken: str = "") -> bool:
+    """True when no run deadlocks or violates an invariant (for a `broken` variant: True means NOT caught)."""
+    for seed in range(runs):
+        sim = Sim(seed)
+        allreduce_split_protocol(sim, world, steps=4, broken=broken)
+        err = sim.run()
+        if err or sim.hazards:
+            if not broken:
+                print(f"[allreduce split world={world} seed={seed}] {err or ''} {'; '.join(sim.hazards[:3])}")
+            return False
+    return True
+
+
+# ---------------------------------------------------------------------------------------------
 # Design study for the next attention forward: two query tiles per CTA, ping-pong (round-2 plan)
 # ---------------------------------------------------------------------------------------------
 class Resource:
@@ -538,5 +692,6 @@ if __name__ == "__main__":
             good &= check(variant, NQ, runs=int(sys.argv[1]) if len(sys.argv) > 1 else 2000)
     for world in (2, 4, 8):
         check_allreduce(world, 200)
+        print(f"allreduce split schedule world={world}:", "no deadlock / hazard in 200 runs" if check_allreduce_split(world) else "FAILED")
     check_fwd_pingpong(200)
     sys.exit(0)  # 'b5' is expected to fail: it documents the hang
